@@ -1,0 +1,136 @@
+/*
+ * tsp.h -- torch-free C-ABI of the B200-native CSR sparse-kernel library (libtsp.so).
+ *
+ * This is the drop-in boundary for the hot path of mabdullahsoyturk/Torch-Sputnik:
+ * every entry point below replaces one call the reference's PyTorch binding makes
+ * into libsputnik / cuSPARSE.  All pointers are DEVICE pointers (fp32 values, int32
+ * indices, row-major dense operands), all launches are asynchronous on `stream`
+ * (a cudaStream_t passed as void*), no entry point synchronises, allocates or keeps
+ * state.  Return value: 0 on success, non-zero on error; tsp_last_error() returns a
+ * thread-local message for the last non-zero return.
+ *
+ * "replicas": the reference loops on the host over the leading dimension of 3-D
+ * operands and launches one kernel per replica (src/spmm_cuda.cu:48-57).  Here the
+ * replica count is an argument and one launch covers all replicas (grid.z).
+ *
+ * Reference interface each entry point replaces (paths relative to /root/reference):
+ *   tsp_spmm_f32            sputnik::CudaSpmm / CudaSpmmBiasRelu
+ *                           third_party/sputnik/sputnik/spmm/cuda_spmm.h:51-72,
+ *                           called from src/spmm_cuda.cu:48-57 (spmm) and
+ *                           src/left_replicated_spmm.cu:32-41 (left_spmm, values shared)
+ *   tsp_sddmm_f32           sputnik::CudaSddmm
+ *                           third_party/sputnik/sputnik/sddmm/cuda_sddmm.h:25-32,
+ *                           called from src/sddmm_cuda.cu:45-54
+ *   tsp_csr_softmax_f32     sputnik::SparseSoftmax
+ *                           third_party/sputnik/sputnik/softmax/sparse_softmax.h:26-32,
+ *                           called from src/softmax_cuda.cu:35-43
+ *   tsp_csr_transpose_f32   cusparseCsr2cscEx2_bufferSize + cusparseCsr2cscEx2 (ALG1)
+ *                           called from src/transpose_cuda.cu:22-31 and :90-99
+ */
+#ifndef TSP_H_
+#define TSP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TSP_VERSION 1
+
+/* Error codes (also the return values). */
+#define TSP_OK 0
+#define TSP_ERR_INVALID_ARGUMENT 1
+#define TSP_ERR_CUDA 2
+#define TSP_ERR_WORKSPACE 3
+
+/* Library version (TSP_VERSION this library was built with). */
+int tsp_version(void);
+
+/* Message for the last error returned on the calling thread ("" if none). */
+const char* tsp_last_error(void);
+
+/*
+ * SpMM:  out[r] = A_r @ dense[r]  (+ bias[:, None], then max(., 0) when relu != 0)
+ *   A_r is the m x k CSR matrix (row_offsets[m+1], column_indices[nnz]) with values
+ *   values + r*nnz  (values_shared == 0: values is [replicas, nnz], spmm 3-D)  or
+ *   values          (values_shared != 0: one [nnz] vector for every replica, left_spmm).
+ *   dense is [replicas, k, n], out is [replicas, m, n]; every element of out is written
+ *   (rows with no nonzeros produce bias/zero), so out may be uninitialised memory.
+ *   row_indices[m] is the row swizzle (any permutation of 0..m-1; work item b handles
+ *   row row_indices[b]).  It may be NULL (identity).  Results do not depend on it.
+ *   bias_or_null: [m] fp32 indexed by OUTPUT ROW (cuda_spmm.cu.cc:267-277), or NULL.
+ *   relu is honoured with or without bias.
+ */
+int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
+                 const int* row_indices, const float* values, const int* row_offsets,
+                 const int* column_indices, const float* dense,
+                 const float* bias_or_null, int relu, float* out, void* stream);
+
+/*
+ * SDDMM: out[r, j] = dot(lhs[r, row_of(j), :], rhs[r, column_indices[j], :])
+ *   lhs is [replicas, m, k], rhs is [replicas, n, k] (i.e. the right operand already
+ *   transposed, as in the reference), out is [replicas, nnz].  Exactly nnz values per
+ *   replica are written.
+ */
+int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas,
+                  const int* row_indices, const int* row_offsets,
+                  const int* column_indices, const float* lhs, const float* rhs,
+                  float* out, void* stream);
+
+/*
+ * CSR softmax: for every row i and replica r, over seg = [row_offsets[i], row_offsets[i+1]):
+ *   out[r, seg] = exp(scale*x - max(scale*x)) / sum(exp(scale*x - max(scale*x))),  x = values[r, seg]
+ *   The reference has no scale (scale = 1.0f); scale folds the caller-side 1/sqrt(d)
+ *   of modules/sparse_attention.py:72 into the same pass.
+ */
+int tsp_csr_softmax_f32(int m, int nnz, int replicas, float scale,
+                        const float* values, const int* row_indices,
+                        const int* row_offsets, float* out, void* stream);
+
+/*
+ * CSR softmax backward: dx[r, seg] = scale * y * (dy - sum(dy * y)),  y = softmax output.
+ * (The reference has no usable gradient for its softmax -- SURVEY.md section 8(f) rank 1.)
+ */
+int tsp_csr_softmax_backward_f32(int m, int nnz, int replicas, float scale,
+                                 const float* y, const float* dy,
+                                 const int* row_indices, const int* row_offsets,
+                                 float* dx, void* stream);
+
+/*
+ * CSR transpose (m x n  ->  n x m), stable in the original nonzero order, which is what
+ * cusparseCsr2cscEx2(CUSPARSE_CSR2CSC_ALG1) returns: inside each output row the entries
+ * appear in ascending original row.  values is [replicas, nnz] (replicas >= 1; the
+ * topology is shared, each replica's values are permuted the same way).
+ *   values_t[replicas, nnz], row_offsets_t[n+1], column_indices_t[nnz] are fully written.
+ *   perm_or_null: if non-NULL receives perm[nnz] with values_t[p] = values[perm[p]]
+ *   (lets a caller cache the permutation of a static topology).
+ *   workspace: device scratch of at least tsp_csr_transpose_workspace(m, n, nnz) bytes,
+ *   256-byte aligned; contents on entry are irrelevant.
+ */
+size_t tsp_csr_transpose_workspace(int m, int n, int nnz);
+int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* values,
+                          const int* row_offsets, const int* column_indices,
+                          float* values_t, int* row_offsets_t, int* column_indices_t,
+                          int* perm_or_null, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* values_t[r, p] = values[r, perm[p]] for a cached permutation (static topology). */
+int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int* perm,
+                           float* values_t, void* stream);
+
+/*
+ * Knobs for A/B benchmarking only (not part of the reference surface):
+ *   tsp_set_variant("spmm", v) / ("sddmm", v): 0 = heuristic (default), other values force
+ *   a kernel variant.  Returns the previous value, or -1 for unknown op.
+ */
+int tsp_set_variant(const char* op, int variant);
+
+/* Number of kernel launches issued by this library on the calling process so far. */
+unsigned long long tsp_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSP_H_ */

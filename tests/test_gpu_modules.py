@@ -1,0 +1,129 @@
+"""GPU: the autograd layer (mirror of the reference's modules/) against dense torch autograd."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import to_dev
+from oracle.csr import dense_operand, random_csr, row_of
+
+pytestmark = pytest.mark.gpu
+
+
+def _dense_from(a, values, dev):
+    r = torch.from_numpy(row_of(a.row_offsets).astype(np.int64)).to(dev)
+    c = torch.from_numpy(a.column_indices.astype(np.int64)).to(dev)
+    lead = values.shape[:-1]
+    out = torch.zeros(*lead, a.m, a.k, dtype=values.dtype, device=dev)
+    out[..., r, c] = values
+    return out, r, c
+
+
+@pytest.mark.parametrize("replicas", [0, 3])
+def test_spmm_function_grads(dev, replicas):
+    from torch_sputnik_b200.modules import Spmm
+    m, k, n = 96, 80, 72
+    a = random_csr(m, k, 0.2, seed=1, values="pm1")
+    v, ri, ro, ci = to_dev(a, dev)
+    lead = (replicas,) if replicas else ()
+    vals = (torch.from_numpy(dense_operand(lead + (a.nnz,), 2, "pm1")).to(dev)).requires_grad_(True)
+    dense = torch.from_numpy(dense_operand(lead + (k, n), 3, "pm1")).to(dev).requires_grad_(True)
+    out = Spmm.apply(m, k, vals, ri, ro, ci, dense)
+    g = torch.from_numpy(dense_operand(tuple(out.shape), 4, "pm1")).to(dev)
+    out.backward(g)
+
+    vals64 = vals.detach().double().requires_grad_(True)
+    dense64 = dense.detach().double().requires_grad_(True)
+    A, r, c = _dense_from(a, vals64, dev)
+    ref = A @ dense64
+    ref.backward(g.double())
+    torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(dense.grad.double(), dense64.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(vals.grad.double(), vals64.grad, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("replicas", [0, 3])
+def test_sddmm_function_grads(dev, replicas):
+    from torch_sputnik_b200.modules import Sddmm
+    m, n, k = 96, 112, 64
+    a = random_csr(m, n, 0.2, seed=5, values="pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    lead = (replicas,) if replicas else ()
+    lhs = torch.from_numpy(dense_operand(lead + (m, k), 6, "pm1")).to(dev).requires_grad_(True)
+    rhs = torch.from_numpy(dense_operand(lead + (n, k), 7, "pm1")).to(dev).requires_grad_(True)
+    out = Sddmm.apply(m, n, ri, ro, ci, lhs, rhs)
+    g = torch.from_numpy(dense_operand(tuple(out.shape), 8, "pm1")).to(dev)
+    out.backward(g)
+    l64, r64 = lhs.detach().double().requires_grad_(True), rhs.detach().double().requires_grad_(True)
+    r = torch.from_numpy(row_of(a.row_offsets).astype(np.int64)).to(dev)
+    c = torch.from_numpy(a.column_indices.astype(np.int64)).to(dev)
+    ref = (l64 @ r64.transpose(-2, -1))[..., r, c]
+    ref.backward(g.double())
+    torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(lhs.grad.double(), l64.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(rhs.grad.double(), r64.grad, rtol=1e-5, atol=1e-5)
+
+
+def test_sparse_linear_matches_pruned_nn_linear(dev):
+    """tests/test_linear_3d.py:100-164: batch 3, W 256x128, 72 tokens; forward and grads within 1e-2
+    of a pruned nn.Linear (here 90 % pruned, checked far tighter)."""
+    from torch_sputnik_b200.modules import SparseLinear
+    torch.manual_seed(0)
+    lin = SparseLinear(128, 256).to(dev)
+    with torch.no_grad():
+        lin.weight.mul_((torch.rand_like(lin.weight) >= 0.9).float())
+    lin.setup_sparse_tensors()
+    x = torch.randn(3, 72, 128, device=dev, requires_grad=True)
+    y = lin(x)                                   # [B, out, tokens] -- transposed, like the reference
+    assert tuple(y.shape) == (3, 256, 72)
+    g = torch.randn_like(y)
+    y.backward(g)
+    w64 = lin.weight.detach().double().requires_grad_(True)
+    x64 = x.detach().double().requires_grad_(True)
+    ref = torch.nn.functional.linear(x64, w64).transpose(1, 2)
+    ref.backward(g.double())
+    torch.testing.assert_close(y.double(), ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(x.grad.double(), x64.grad, rtol=1e-5, atol=1e-5)
+    r = torch.from_numpy(row_of(lin.row_offsets.cpu().numpy()).astype(np.int64)).to(dev)
+    c = lin.column_indices.long()
+    torch.testing.assert_close(lin.values.grad.double(), w64.grad[r, c], rtol=1e-5, atol=1e-4)
+
+
+def test_sparse_attention_matches_dense_masked_attention(dev):
+    """modules/sparse_attention.py:57-98 pipeline (SDDMM -> scale -> softmax -> SpMM), with a real
+    softmax gradient, against dense masked attention in fp64."""
+    from torch_sputnik_b200.modules import SparseAttention
+    torch.manual_seed(1)
+    b, h, s, d = 2, 4, 128, 32
+    att = SparseAttention(h, h * d, max_sequence_length=s, sparsity=0.8, device=dev, seed=3).to(dev)
+    q, k, v = (torch.randn(b, h, s, d, device=dev, requires_grad=True) for _ in range(3))
+    out = att.attention(q, k, v)
+    assert tuple(out.shape) == (b * h, s, d)
+    g = torch.randn_like(out)
+    out.backward(g)
+    mask = att.mask2d.bool()
+    # no row of the mask may be empty for the dense comparison
+    assert bool(mask.any(dim=1).all())
+    q64, k64, v64 = (t.detach().double().requires_grad_(True) for t in (q, k, v))
+    scores = (q64 @ k64.transpose(-2, -1)) / math.sqrt(d)
+    scores = scores.masked_fill(~mask, float("-inf"))
+    ref = (torch.softmax(scores, dim=-1) @ v64).reshape(b * h, s, d)
+    ref.backward(g.double())
+    torch.testing.assert_close(out.double(), ref, rtol=1e-4, atol=1e-5)
+    for got, want in ((q.grad, q64.grad), (k.grad, k64.grad), (v.grad, v64.grad)):
+        torch.testing.assert_close(got.double(), want, rtol=1e-4, atol=1e-5)
+
+
+def test_sparse_attention_module_forward_backward_runs(dev):
+    from torch_sputnik_b200.modules import SparseAttention
+    torch.manual_seed(2)
+    att = SparseAttention(4, 128, max_sequence_length=64, sparsity=0.75, device=dev, seed=4).to(dev)
+    att.prune_and_setup(seed=0)
+    x = torch.randn(2, 64, 128, device=dev, requires_grad=True)
+    y = att(x, x, x)
+    assert tuple(y.shape) == (2, 128, 64)
+    y.square().mean().backward()
+    assert x.grad is not None and torch.isfinite(x.grad).all()
+    for lin in att.linears:
+        assert lin.values.grad is not None and torch.isfinite(lin.values.grad).all()

@@ -1,0 +1,145 @@
+"""GPU parity: CUDA SDDMM vs the oracle."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from helpers import ABS_SPUTNIK, assert_close_fwd, to_dev
+from oracle.csr import dense_operand, random_csr, row_of
+
+pytestmark = pytest.mark.gpu
+
+# third_party/sputnik/sputnik/sddmm/sddmm_test.cu.cc:76-91  (m, k, n, nnz)
+SPUTNIK_SDDMM_PROBLEMS = [
+    (1, 32, 32, 32), (1, 64, 32, 32), (1, 32, 64, 64), (1, 32, 64, 32), (1, 32, 64, 16),
+    (2, 32, 32, 64), (1024, 80, 1024, 131072), (1, 28, 32, 32), (1024, 128, 1024, 131072),
+    (1024, 256, 1024, 131072), (1024, 512, 1024, 131072), (2048, 128, 2048, 1024 * 1024),
+    (2048 * 3, 128, 2048, 1024 * 1024 * 3), (2048 * 4, 128, 2048, 1024 * 1024 * 4),
+]
+
+
+def check_sddmm(ops, dev, a, lhs, rhs, what):
+    _, ri, ro, ci = to_dev(a, dev)
+    got = ops.sddmm(a.m, a.k, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev))
+    got = got.cpu().numpy()
+    ref = oracle.sddmm(a.m, a.k, a.row_offsets, a.column_indices, lhs, rhs)
+    scale = oracle.sddmm_abs(a.m, a.k, a.row_offsets, a.column_indices, lhs, rhs)
+    assert got.shape == ref.shape
+    assert_close_fwd(got, ref, scale, what=what)
+    return got, ref
+
+
+@pytest.mark.parametrize("m,k,n,nnz", SPUTNIK_SDDMM_PROBLEMS)
+def test_sddmm_sputnik_problem_list(ops, dev, m, k, n, nnz):
+    a = random_csr(m, n, nnz=nnz, seed=k + n, values="pm1")
+    lhs, rhs = dense_operand((m, k), 1, "pm1"), dense_operand((n, k), 2, "pm1")
+    got, ref = check_sddmm(ops, dev, a, lhs, rhs, f"sddmm {m}x{k}x{n}/{nnz}")
+    assert np.max(np.abs(got - ref)) < ABS_SPUTNIK    # sddmm_test.cu.cc:141
+
+
+def test_sddmm_reference_test_shape(ops, dev):
+    """tests/test_sddmm.py:16-37: 72x64x72, full mask, (lhs @ rhs^T) within 1e-4."""
+    a = random_csr(72, 72, 1.0, seed=0, values="u01")
+    lhs, rhs = dense_operand((72, 64), 1, "u01"), dense_operand((72, 64), 2, "u01")
+    got, _ = check_sddmm(ops, dev, a, lhs, rhs, "72x64x72 full")
+    dense = oracle.dense_sddmm(lhs, rhs, np.ones((72, 72), np.float32)).numpy()
+    assert np.all(np.abs(got.reshape(72, 72) - dense) < 1e-4 * 4)
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 5, 7, 8, 12, 16, 28, 31, 32, 36, 63, 64, 65, 100, 128, 132, 257, 1000])
+def test_sddmm_ragged_k(ops, dev, k):
+    a = random_csr(45, 77, 0.25, seed=k, values="pm1")
+    check_sddmm(ops, dev, a, dense_operand((45, k), 3, "pm1"), dense_operand((77, k), 4, "pm1"), f"k={k}")
+
+
+@pytest.mark.parametrize("density", [0.0, 0.003, 0.5, 1.0])
+def test_sddmm_density_extremes(ops, dev, density):
+    a = random_csr(130, 97, density, seed=5, values="pm1")
+    if a.nnz == 0:
+        _, ri, ro, ci = to_dev(a, dev)
+        out = ops.sddmm(130, 97, ri, ro, ci, torch.zeros(130, 64, device=dev), torch.zeros(97, 64, device=dev))
+        assert tuple(out.shape) == (0,)
+        return
+    check_sddmm(ops, dev, a, dense_operand((130, 64), 6, "pm1"), dense_operand((97, 64), 7, "pm1"), f"d={density}")
+
+
+def test_sddmm_replicated_3d_and_quirks(ops, dev):
+    """src/sddmm_cuda.cu:43: [R, nnz] for R > 1, 1-D when the replica count is 1."""
+    R, m, n, k = 4, 72, 72, 64
+    a = random_csr(m, n, 0.1, seed=8, values="u01", round_to=4)
+    lhs, rhs = dense_operand((R, m, k), 9, "pm1"), dense_operand((R, n, k), 10, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    got = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev))
+    assert tuple(got.shape) == (R, a.nnz)
+    ref = oracle.sddmm(m, n, a.row_offsets, a.column_indices, lhs, rhs)
+    for r in range(R):
+        scale = oracle.sddmm_abs(m, n, a.row_offsets, a.column_indices, lhs[r], rhs[r])
+        assert_close_fwd(got[r].cpu().numpy(), ref[r], scale, what=f"replica {r}")
+    one = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs[:1]).to(dev), torch.from_numpy(rhs[:1]).to(dev))
+    assert tuple(one.shape) == (a.nnz,)
+
+
+@pytest.mark.parametrize("variant", [1, 2])
+def test_sddmm_variants_agree(ops, dev, variant):
+    a = random_csr(512, 640, 0.15, seed=11, values="pm1")
+    prev = ops.set_variant("sddmm", variant)
+    try:
+        check_sddmm(ops, dev, a, dense_operand((512, 256), 12, "pm1"), dense_operand((640, 256), 13, "pm1"),
+                    f"variant {variant}")
+    finally:
+        ops.set_variant("sddmm", prev)
+
+
+def test_sddmm_attention_shape(ops, dev):
+    """BASELINE.json configs[3] shape per replica: s=4096, d=64, 90 % sparse; 2 replicas here."""
+    a = random_csr(4096, 4096, 0.1, seed=14, values="u01")
+    lhs, rhs = dense_operand((2, 4096, 64), 15, "pm1"), dense_operand((2, 4096, 64), 16, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    got = ops.sddmm(4096, 4096, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev))
+    ref = oracle.sddmm(4096, 4096, a.row_offsets, a.column_indices, lhs, rhs)
+    for r in range(2):
+        scale = oracle.sddmm_abs(4096, 4096, a.row_offsets, a.column_indices, lhs[r], rhs[r])
+        assert_close_fwd(got[r].cpu().numpy(), ref[r], scale, what=f"attention replica {r}")
+
+
+@pytest.mark.parametrize("density", [0.05, 0.25])
+def test_sddmm_4096_full_oracle(ops, dev, density):
+    a = random_csr(4096, 4096, density, seed=0, values="pm1")
+    check_sddmm(ops, dev, a, dense_operand((4096, 4096), 1, "pm1"), dense_operand((4096, 4096), 2, "pm1"),
+                f"4096^3 d={density}")
+
+
+def test_sddmm_4096_half_density_properties(ops, dev):
+    """d = 0.5 at full size: ones x ones = k exactly, and sampled nonzeros against fp64."""
+    m = n = k = 4096
+    a = random_csr(m, n, 0.5, seed=1, values="pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    out = ops.sddmm(m, n, ri, ro, ci, torch.ones(m, k, device=dev), torch.ones(n, k, device=dev))
+    assert bool((out == float(k)).all())
+    lhs, rhs = dense_operand((m, k), 3, "pm1"), dense_operand((n, k), 4, "pm1")
+    got = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev)).cpu().numpy()
+    pick = np.random.default_rng(2).choice(a.nnz, 20000, replace=False)
+    rows, cols = row_of(a.row_offsets)[pick], a.column_indices[pick]
+    l64, r64 = lhs[rows].astype(np.float64), rhs[cols].astype(np.float64)
+    ref = np.einsum("ij,ij->i", l64, r64)
+    scale = np.einsum("ij,ij->i", np.abs(l64), np.abs(r64))
+    assert_close_fwd(got[pick], ref, scale, what="sampled nonzeros")
+
+
+def test_sddmm_through_raw_c_abi(dev):
+    from torch_sputnik_b200 import cabi
+    lib = cabi.load()
+    a = random_csr(150, 170, 0.2, seed=17, values="pm1")
+    lhs, rhs = dense_operand((150, 96), 18, "pm1"), dense_operand((170, 96), 19, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    ld, rd = torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev)
+    out = torch.full((a.nnz,), float("nan"), device=dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    rc = lib.tsp_sddmm_f32(150, 96, 170, a.nnz, 1, p(ri), p(ro), p(ci), p(ld), p(rd), p(out),
+                           ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, cabi.last_error()
+    ref = oracle.sddmm(150, 170, a.row_offsets, a.column_indices, lhs, rhs)
+    scale = oracle.sddmm_abs(150, 170, a.row_offsets, a.column_indices, lhs, rhs)
+    assert_close_fwd(out.cpu().numpy(), ref, scale, what="c-abi")

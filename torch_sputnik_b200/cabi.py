@@ -1,0 +1,45 @@
+"""ctypes binding of the C-ABI (include/tsp.h) -- for tests and harnesses that want to call
+libtsp.so directly with raw device pointers, without going through the torch shim."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libtsp.so")
+
+# Every symbol include/tsp.h declares.
+SYMBOLS = (
+    "tsp_version", "tsp_last_error", "tsp_spmm_f32", "tsp_sddmm_f32", "tsp_csr_softmax_f32",
+    "tsp_csr_softmax_backward_f32", "tsp_csr_transpose_workspace", "tsp_csr_transpose_f32",
+    "tsp_permute_values_f32", "tsp_set_variant", "tsp_launch_count",
+)
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} not built; run `python -m torch_sputnik_b200.build`")
+        lib = ctypes.CDLL(LIB_PATH)
+        i, vp, f, sz = ctypes.c_int, ctypes.c_void_p, ctypes.c_float, ctypes.c_size_t
+        lib.tsp_version.restype = i
+        lib.tsp_last_error.restype = ctypes.c_char_p
+        lib.tsp_spmm_f32.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, i, vp, vp]
+        lib.tsp_sddmm_f32.argtypes = [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
+        lib.tsp_csr_softmax_f32.argtypes = [i, i, i, f, vp, vp, vp, vp, vp]
+        lib.tsp_csr_softmax_backward_f32.argtypes = [i, i, i, f, vp, vp, vp, vp, vp, vp]
+        lib.tsp_csr_transpose_workspace.argtypes = [i, i, i]
+        lib.tsp_csr_transpose_workspace.restype = sz
+        lib.tsp_csr_transpose_f32.argtypes = [i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
+        lib.tsp_permute_values_f32.argtypes = [i, i, vp, vp, vp, vp]
+        lib.tsp_set_variant.argtypes = [ctypes.c_char_p, i]
+        lib.tsp_launch_count.restype = ctypes.c_ulonglong
+        _lib = lib
+    return _lib
+
+
+def last_error() -> str:
+    return load().tsp_last_error().decode()

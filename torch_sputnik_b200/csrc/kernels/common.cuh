@@ -1,0 +1,121 @@
+// common.cuh -- shared device/host helpers for the tsp kernels (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "tsp kernels are written for sm_100a (B200) only"
+#endif
+
+namespace tsp {
+
+constexpr int kWarp = 32;
+constexpr unsigned kFullMask = 0xffffffffu;
+
+// ---------------------------------------------------------------- host side
+void set_error(const char* fmt, ...);  // defined in tsp_abi.cu (thread-local message)
+extern std::atomic<unsigned long long> g_launches;
+
+inline int cuda_fail(cudaError_t e, const char* what) {
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return 2;  // TSP_ERR_CUDA
+}
+
+#define TSP_CHECK_LAUNCH(what)                                  \
+  do {                                                          \
+    ::tsp::g_launches.fetch_add(1, std::memory_order_relaxed);  \
+    cudaError_t e__ = cudaGetLastError();                       \
+    if (e__ != cudaSuccess) return ::tsp::cuda_fail(e__, what); \
+  } while (0)
+
+inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+int sm_count();  // cached cudaDevAttrMultiProcessorCount of the current device
+
+// -------------------------------------------------------------- device side
+#ifdef __CUDACC__
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+// Read-only (non-coherent) loads: operands are never written by the same kernel.
+__device__ __forceinline__ float ldg_f(const float* p) { return __ldg(p); }
+__device__ __forceinline__ int ldg_i(const int* p) { return __ldg(p); }
+__device__ __forceinline__ float4 ldg_f4(const float* p) {
+  return __ldg(reinterpret_cast<const float4*>(p));
+}
+
+// Streaming loads/stores for data touched exactly once (keeps L1/L2 for the gathered operand).
+__device__ __forceinline__ float ld_stream_f(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_stream_f(float* p, float v) {
+  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_stream_f4(float* p, float4 v) {
+  asm volatile("st.global.cs.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+// Packed 2 x fp32 FMA (SASS FFMA2 on sm_100a): d = a * b + c lane-wise on register pairs.
+// Same per-lane IEEE rounding as FFMA; halves the issue slots of the FMA stream.
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b0,
+                                      float b1) {
+  unsigned long long a, b, c;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(d0), "f"(d1));
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(c) : "l"(a), "l"(b));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(c));
+}
+
+// Butterflies run 1,2,4,8,16 -- the order of sparse_softmax.cu.cc:46-49,57-59 -- so sums round
+// the same way as the reference's.
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) v = fmaxf(v, __shfl_xor_sync(kFullMask, v, s));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) v += __shfl_xor_sync(kFullMask, v, s);
+  return v;
+}
+
+// cp.async (LDGSTS) 16-byte copy global -> shared, L2-only (.cg) so the staged tile
+// does not pollute L1.
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+#endif  // __CUDACC__
+
+}  // namespace tsp

@@ -1,0 +1,203 @@
+// csr_transpose.cuh -- stable CSR -> CSC (= CSR of the transpose), bit-exact, no atomics in the
+// placement.
+//
+// Replaces cusparseCsr2cscEx2(..., CUSPARSE_CSR2CSC_ALG1) as called from
+// src/transpose_cuda.cu:90-99.  ALG1 is a stable sort of the nonzeros by column, so inside
+// every output row the entries keep ascending original-row order; an atomic scatter would not
+// reproduce that.  Here: a stable LSD radix sort of the flat nonzero index keyed by column
+// (ceil(log2 n) bits in ceil(bits/8) passes), each pass = per-tile digit histogram -> one
+// exclusive scan of the [digit][tile] table -> stable in-tile ranking with warp match + ordered
+// per-warp counters.  A last kernel turns the sorted order into values_t / column_indices_t /
+// row_offsets_t / perm.
+#pragma once
+#include "common.cuh"
+
+namespace tsp {
+
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kSortItems = 16;                          // per thread
+constexpr int kSortTile = kSortThreads * kSortItems;    // 4096 keys per CTA
+constexpr int kSortWarpSeg = 32 * kSortItems;           // 512 consecutive keys per warp
+constexpr int kMaxRadix = 256;
+
+struct SortPlan {
+  int bits, passes, digit_bits, radix, tiles;
+};
+
+inline SortPlan make_sort_plan(int n, int nnz) {
+  SortPlan p;
+  int bits = 1;
+  while (bits < 31 && (1LL << bits) < (long long)n) ++bits;
+  p.bits = bits;
+  p.passes = (bits + 7) / 8;
+  p.digit_bits = (bits + p.passes - 1) / p.passes;
+  p.radix = 1 << p.digit_bits;
+  p.tiles = nnz > 0 ? (nnz + kSortTile - 1) / kSortTile : 0;
+  return p;
+}
+
+// hist[d * tiles + tile] = number of keys of `tile` whose digit is d.
+__global__ void __launch_bounds__(kSortThreads)
+radix_hist_kernel(const int* __restrict__ keys, int nnz, int shift, int radix, int tiles,
+                  int* __restrict__ hist) {
+  __shared__ int s_hist[kMaxRadix];
+  for (int d = threadIdx.x; d < radix; d += kSortThreads) s_hist[d] = 0;
+  __syncthreads();
+  const int tile = blockIdx.x;
+  const int base = tile * kSortTile;
+  const int mask = radix - 1;
+#pragma unroll 4
+  for (int i = 0; i < kSortItems; ++i) {
+    const int e = base + i * kSortThreads + threadIdx.x;
+    if (e < nnz) atomicAdd(&s_hist[(__ldg(keys + e) >> shift) & mask], 1);
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < radix; d += kSortThreads) hist[(size_t)d * tiles + tile] = s_hist[d];
+}
+
+// In-place exclusive scan of `count` ints by one CTA (count = radix * tiles; a few 100k at most).
+__global__ void __launch_bounds__(1024) exclusive_scan_kernel(int* __restrict__ data, int count) {
+  __shared__ int s_warp[32];
+  __shared__ int s_carry;
+  const int tid = threadIdx.x;
+  const int per = (count + 1023) / 1024;
+  const int beg = min(count, tid * per), end = min(count, beg + per);
+  int sum = 0;
+  for (int i = beg; i < end; ++i) sum += data[i];
+  // block exclusive scan of `sum`
+  int incl = sum;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const int t = __shfl_up_sync(kFullMask, incl, s);
+    if ((tid & 31) >= s) incl += t;
+  }
+  if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+  __syncthreads();
+  if (tid < 32) {
+    int w = s_warp[tid];
+    int wi = w;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const int t = __shfl_up_sync(kFullMask, wi, s);
+      if (tid >= s) wi += t;
+    }
+    s_warp[tid] = wi - w;
+    if (tid == 31) s_carry = wi;
+  }
+  __syncthreads();
+  int run = s_warp[tid >> 5] + incl - sum;
+  for (int i = beg; i < end; ++i) {
+    const int v = data[i];
+    data[i] = run;
+    run += v;
+  }
+  (void)s_carry;
+}
+
+// Stable scatter of one radix pass.  Order inside a tile: warp-major, then round, then lane.
+// payload_in == nullptr means the identity payload (first pass).
+__global__ void __launch_bounds__(kSortThreads)
+radix_scatter_kernel(const int* __restrict__ keys_in, const int* __restrict__ payload_in, int nnz,
+                     int shift, int radix, int tiles, const int* __restrict__ hist_scanned,
+                     int* __restrict__ keys_out, int* __restrict__ payload_out) {
+  __shared__ int s_cnt[kSortWarps][kMaxRadix];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x;
+  const int mask = radix - 1;
+  for (int d = lane; d < radix; d += 32) s_cnt[warp][d] = 0;
+  __syncwarp();
+
+  const int seg = tile * kSortTile + warp * kSortWarpSeg;
+  int key[kSortItems], rank[kSortItems];
+  const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int i = 0; i < kSortItems; ++i) {
+    const int e = seg + i * 32 + lane;
+    const bool in = e < nnz;
+    key[i] = in ? __ldg(keys_in + e) : 0;
+    const int d = in ? ((key[i] >> shift) & mask) : radix;  // radix = "no key" class
+    const unsigned peers = __match_any_sync(kFullMask, d);
+    int before = 0;
+    if (in) before = s_cnt[warp][d];
+    __syncwarp();
+    if (in && (peers & lt) == 0) s_cnt[warp][d] = before + __popc(peers);
+    __syncwarp();
+    rank[i] = before + __popc(peers & lt);
+  }
+  __syncthreads();
+  // Exclusive prefix over warps per digit, plus the global base of (digit, tile).
+  for (int d = threadIdx.x; d < radix; d += kSortThreads) {
+    int run = __ldg(hist_scanned + (size_t)d * tiles + tile);
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {
+      const int c = s_cnt[w][d];
+      s_cnt[w][d] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < kSortItems; ++i) {
+    const int e = seg + i * 32 + lane;
+    if (e < nnz) {
+      const int d = (key[i] >> shift) & mask;
+      const int pos = s_cnt[warp][d] + rank[i];
+      keys_out[pos] = key[i];
+      payload_out[pos] = payload_in ? __ldg(payload_in + e) : e;
+    }
+  }
+}
+
+struct TransposeFinishArgs {
+  int m, n, nnz, replicas;
+  const int* sorted_cols;   // [nnz] ascending
+  const int* sorted_src;    // [nnz] original flat index of each sorted entry
+  const int* row_offsets;   // [m+1] of the input
+  const float* values;      // [replicas, nnz]
+  float* values_t;          // [replicas, nnz]
+  int* row_offsets_t;       // [n+1]
+  int* column_indices_t;    // [nnz]
+  int* perm;                // may be null
+};
+
+__device__ __forceinline__ int upper_row(const int* __restrict__ row_offsets, int m, int j) {
+  int lo = 0, hi = m;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(row_offsets + mid) <= j) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// One thread per sorted position p (plus one extra thread p == nnz closing the offsets).
+__global__ void __launch_bounds__(256) transpose_finish_kernel(const TransposeFinishArgs a) {
+  const int p = blockIdx.x * 256 + threadIdx.x;
+  if (p > a.nnz) return;
+  const int c = p < a.nnz ? __ldg(a.sorted_cols + p) : a.n;
+  const int cprev = p > 0 ? __ldg(a.sorted_cols + p - 1) : -1;
+  // Output rows cprev+1 .. c start at p (empty output rows collapse onto the same offset).
+  for (int r = cprev + 1; r <= c; ++r) a.row_offsets_t[r] = p;
+  if (p == a.nnz) return;
+  const int src = __ldg(a.sorted_src + p);
+  a.column_indices_t[p] = upper_row(a.row_offsets, a.m, src);
+  if (a.perm) a.perm[p] = src;
+  for (int r = 0; r < a.replicas; ++r)
+    a.values_t[(size_t)r * a.nnz + p] = __ldg(a.values + (size_t)r * a.nnz + src);
+}
+
+__global__ void __launch_bounds__(256)
+permute_values_kernel(int nnz, const float* __restrict__ values, const int* __restrict__ perm,
+                      float* __restrict__ values_t) {
+  const int p = blockIdx.x * 256 + threadIdx.x;
+  if (p >= nnz) return;
+  const size_t base = (size_t)blockIdx.y * nnz;
+  values_t[base + p] = __ldg(values + base + __ldg(perm + p));
+}
+
+__global__ void fill_int_kernel(int* __restrict__ dst, int count, int value) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < count) dst[i] = value;
+}
+
+}  // namespace tsp

@@ -1,0 +1,323 @@
+// torch_shim.cpp -- the `torch_sputnik` Python module, rebuilt as a thin shim over libtsp.so.
+//
+// Same module name, op names, positional signatures, return shapes and dtypes as the reference
+// binding (src/sputnik.cpp:36-42 of mabdullahsoyturk/Torch-Sputnik), so the reference's
+// autograd Functions (modules/spmm.py, sddmm.py, sparse_linear.py, sparse_attention.py) run
+// unchanged.  What lives here: shape bookkeeping and the reference's quirks, argument checks
+// (TORCH_CHECK -> RuntimeError; the reference uses bare asserts and aborts the process through
+// glog on a CUDA error, include/error_check.h:5-17), output allocation with torch::empty (every
+// element is written by the kernels, so the reference's torch::zeros pre-clear is dropped), a
+// device guard, and the current-stream lookup.  All arithmetic is behind the C-ABI of
+// include/tsp.h; there is no CPU or library fallback.
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/extension.h>
+
+#include <vector>
+
+#include "../../include/tsp.h"
+
+namespace {
+
+#define TSP_CHECK_CUDA_F32(t, name)                                                          \
+  TORCH_CHECK((t).is_cuda(), "torch_sputnik: ", name, " must be a CUDA tensor");             \
+  TORCH_CHECK((t).scalar_type() == torch::kFloat32, "torch_sputnik: ", name,                 \
+              " must be float32, got ", (t).scalar_type());                                  \
+  TORCH_CHECK((t).is_contiguous(), "torch_sputnik: ", name, " must be contiguous")
+
+#define TSP_CHECK_CUDA_I32(t, name)                                                          \
+  TORCH_CHECK((t).is_cuda(), "torch_sputnik: ", name, " must be a CUDA tensor");             \
+  TORCH_CHECK((t).scalar_type() == torch::kInt32, "torch_sputnik: ", name,                   \
+              " must be int32, got ", (t).scalar_type());                                    \
+  TORCH_CHECK((t).is_contiguous(), "torch_sputnik: ", name, " must be contiguous")
+
+void check_rc(int rc, const char* op) {
+  TORCH_CHECK(rc == TSP_OK, "torch_sputnik.", op, " failed (", rc, "): ", tsp_last_error());
+}
+
+// modules/sparse_linear.py:5-7,57 hands an int64 row_indices to left_spmm in backward; the
+// reference's data_ptr<int>() would throw.  Accept it and narrow.
+torch::Tensor as_i32_indices(const torch::Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda(), "torch_sputnik: ", name, " must be a CUDA tensor");
+  if (t.scalar_type() == torch::kInt64) return t.to(torch::kInt32).contiguous();
+  TORCH_CHECK(t.scalar_type() == torch::kInt32, "torch_sputnik: ", name,
+              " must be int32 (or int64), got ", t.scalar_type());
+  return t.contiguous();
+}
+
+void* current_stream() { return static_cast<void*>(at::cuda::getCurrentCUDAStream().stream()); }
+
+void check_topology(int64_t m, const torch::Tensor& row_indices, const torch::Tensor& row_offsets,
+                    const torch::Tensor& column_indices) {
+  TORCH_CHECK(row_indices.dim() == 1, "torch_sputnik: row_indices must have 1 dimension");
+  TORCH_CHECK(row_offsets.dim() == 1, "torch_sputnik: row_offsets must have 1 dimension");
+  TORCH_CHECK(column_indices.dim() == 1, "torch_sputnik: column_indices must have 1 dimension");
+  TORCH_CHECK(row_indices.size(0) == m, "torch_sputnik: expected ", m, " row_indices, got ",
+              row_indices.size(0));
+  TORCH_CHECK(row_offsets.size(0) == m + 1, "torch_sputnik: expected ", m + 1,
+              " row_offsets, got ", row_offsets.size(0));
+  TSP_CHECK_CUDA_I32(row_offsets, "row_offsets");
+  TSP_CHECK_CUDA_I32(column_indices, "column_indices");
+}
+
+// Shared body of spmm / left_spmm / spmm_bias_relu.
+torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values,
+                        const torch::Tensor& row_indices_in, const torch::Tensor& row_offsets,
+                        const torch::Tensor& column_indices, const torch::Tensor& dense,
+                        const c10::optional<torch::Tensor>& bias, bool relu, bool left,
+                        const char* op) {
+  TORCH_CHECK(values.dim() == 1 || values.dim() == 2, "torch_sputnik.", op,
+              ": values must have 1 or 2 dimensions");
+  TORCH_CHECK(dense.dim() == 2 || dense.dim() == 3, "torch_sputnik.", op,
+              ": dense must have 2 or 3 dimensions");
+  TSP_CHECK_CUDA_F32(values, "values");
+  TSP_CHECK_CUDA_F32(dense, "dense");
+  c10::cuda::CUDAGuard guard(values.device());
+  torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
+  check_topology(m, row_indices, row_offsets, column_indices);
+
+  const int64_t nnz = column_indices.size(0);
+  const int dim_offset = dense.dim() - 2;
+  const int64_t replicas = dim_offset == 1 ? dense.size(0) : 1;
+  const int64_t n = dense.size(dim_offset + 1);
+  TORCH_CHECK(dense.size(dim_offset) == k, "torch_sputnik.", op,
+              ": inner dimensions must match (dense has ", dense.size(dim_offset), " rows, k=", k, ")");
+  TORCH_CHECK(values.size(-1) == nnz, "torch_sputnik.", op,
+              ": number of values must equal number of column indices");
+  bool shared = left || values.dim() == 1;
+  if (!shared)
+    TORCH_CHECK(values.size(0) == replicas, "torch_sputnik.", op,
+                ": first dims of values and dense must match");
+  if (left) TORCH_CHECK(values.dim() == 1, "torch_sputnik.left_spmm: values must be 1-D");
+
+  const float* bias_ptr = nullptr;
+  torch::Tensor bias_t;
+  if (bias.has_value()) {
+    bias_t = *bias;
+    TSP_CHECK_CUDA_F32(bias_t, "bias");
+    TORCH_CHECK(bias_t.dim() == 1 && bias_t.size(0) == m, "torch_sputnik.", op,
+                ": bias must have m elements (it is indexed by output row)");
+    bias_ptr = bias_t.data_ptr<float>();
+  }
+
+  auto options = torch::TensorOptions().dtype(torch::kFloat32).device(values.device());
+  // Reference quirk: `spmm` returns 2-D whenever the replica count is 1 (src/spmm_cuda.cu:46);
+  // `left_spmm` is always 3-D (src/left_replicated_spmm.cu:30).
+  torch::Tensor out = (left || replicas != 1) ? torch::empty({replicas, m, n}, options)
+                                              : torch::empty({m, n}, options);
+  check_rc(tsp_spmm_f32((int)m, (int)k, (int)n, (int)nnz, (int)replicas, shared ? 1 : 0,
+                        row_indices.data_ptr<int>(), values.data_ptr<float>(),
+                        row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                        dense.data_ptr<float>(), bias_ptr, relu ? 1 : 0, out.data_ptr<float>(),
+                        current_stream()),
+           op);
+  return out;
+}
+
+}  // namespace
+
+// src/sputnik.cpp:4-9 -> src/spmm_cuda.cu:9-60
+torch::Tensor spmm(int m, int k, torch::Tensor values, torch::Tensor row_indices,
+                   torch::Tensor row_offsets, torch::Tensor column_indices, torch::Tensor dense) {
+  return spmm_impl(m, k, values, row_indices, row_offsets, column_indices, dense, c10::nullopt,
+                   false, false, "spmm");
+}
+
+// src/sputnik.cpp:11-16 -> src/left_replicated_spmm.cu:8-44
+torch::Tensor left_spmm(int m, int k, torch::Tensor values, torch::Tensor row_indices,
+                        torch::Tensor row_offsets, torch::Tensor column_indices,
+                        torch::Tensor dense) {
+  return spmm_impl(m, k, values, row_indices, row_offsets, column_indices, dense, c10::nullopt,
+                   false, true, "left_spmm");
+}
+
+// The op tests/test_spmm_bias_relu.py:37 calls (`spmm_bias`) but the reference never bound:
+// sputnik::CudaSpmmBiasRelu, out = max(A @ dense + bias[:, None], 0).
+torch::Tensor spmm_bias_relu(int m, int k, torch::Tensor values, torch::Tensor row_indices,
+                             torch::Tensor row_offsets, torch::Tensor column_indices,
+                             torch::Tensor bias, torch::Tensor dense) {
+  return spmm_impl(m, k, values, row_indices, row_offsets, column_indices, dense, bias, true,
+                   false, "spmm_bias_relu");
+}
+
+// src/sputnik.cpp:18-23 -> src/sddmm_cuda.cu:7-57
+torch::Tensor sddmm(int m, int n, torch::Tensor row_indices_in, torch::Tensor row_offsets,
+                    torch::Tensor column_indices, torch::Tensor lhs, torch::Tensor rhs) {
+  TORCH_CHECK(lhs.dim() == 2 || lhs.dim() == 3, "torch_sputnik.sddmm: lhs must be 2-D or 3-D");
+  TORCH_CHECK(lhs.dim() == rhs.dim(), "torch_sputnik.sddmm: lhs and rhs must have the same rank");
+  TSP_CHECK_CUDA_F32(lhs, "lhs_matrix");
+  TSP_CHECK_CUDA_F32(rhs, "rhs_matrix");
+  c10::cuda::CUDAGuard guard(lhs.device());
+  torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
+  check_topology(m, row_indices, row_offsets, column_indices);
+  TORCH_CHECK(lhs.size(-1) == rhs.size(-1), "torch_sputnik.sddmm: last dims of lhs and rhs must match");
+
+  const int64_t nnz = column_indices.size(0);
+  const int dim_offset = lhs.dim() - 2;
+  const int64_t replicas = dim_offset == 1 ? lhs.size(0) : 1;
+  const int64_t k = lhs.size(dim_offset + 1);
+  TORCH_CHECK(lhs.size(dim_offset) == m, "torch_sputnik.sddmm: lhs must have m rows");
+  TORCH_CHECK(rhs.size(dim_offset) == n, "torch_sputnik.sddmm: rhs must have n rows");
+  TORCH_CHECK(dim_offset == 0 || rhs.size(0) == replicas,
+              "torch_sputnik.sddmm: first dims of lhs and rhs must match");
+
+  auto options = torch::TensorOptions().dtype(torch::kFloat32).device(lhs.device());
+  torch::Tensor out = replicas == 1 ? torch::empty({nnz}, options)
+                                    : torch::empty({replicas, nnz}, options);
+  check_rc(tsp_sddmm_f32(m, (int)k, n, (int)nnz, (int)replicas, row_indices.data_ptr<int>(),
+                         row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                         lhs.data_ptr<float>(), rhs.data_ptr<float>(), out.data_ptr<float>(),
+                         current_stream()),
+           "sddmm");
+  return out;
+}
+
+static torch::Tensor softmax_impl(const torch::Tensor& values, const torch::Tensor& row_indices_in,
+                                  const torch::Tensor& row_offsets,
+                                  const torch::Tensor& column_indices, double scale) {
+  TORCH_CHECK(values.dim() == 1 || values.dim() == 2,
+              "torch_sputnik.sparse_softmax: values must have 1 or 2 dimensions");
+  TSP_CHECK_CUDA_F32(values, "values");
+  c10::cuda::CUDAGuard guard(values.device());
+  torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
+  const int64_t m = row_indices.size(0);
+  check_topology(m, row_indices, row_offsets, column_indices);
+  const int64_t nnz = column_indices.size(0);
+  TORCH_CHECK(values.size(-1) == nnz,
+              "torch_sputnik.sparse_softmax: number of values must equal number of column indices");
+  const int64_t replicas = values.dim() == 2 ? values.size(0) : 1;
+  torch::Tensor out = torch::empty_like(values);
+  check_rc(tsp_csr_softmax_f32((int)m, (int)nnz, (int)replicas, (float)scale,
+                               values.data_ptr<float>(), row_indices.data_ptr<int>(),
+                               row_offsets.data_ptr<int>(), out.data_ptr<float>(), current_stream()),
+           "sparse_softmax");
+  return out;
+}
+
+// src/sputnik.cpp:25-28 -> src/softmax_cuda.cu:7-46
+torch::Tensor sparse_softmax(torch::Tensor values, torch::Tensor row_indices,
+                             torch::Tensor row_offsets, torch::Tensor column_indices) {
+  return softmax_impl(values, row_indices, row_offsets, column_indices, 1.0);
+}
+
+// Extension: softmax(scale * x) in one pass (folds modules/sparse_attention.py:72).
+torch::Tensor sparse_softmax_scaled(torch::Tensor values, torch::Tensor row_indices,
+                                    torch::Tensor row_offsets, torch::Tensor column_indices,
+                                    double scale) {
+  return softmax_impl(values, row_indices, row_offsets, column_indices, scale);
+}
+
+// Extension: dx = scale * y * (dy - rowsum(dy * y)).
+torch::Tensor sparse_softmax_backward(torch::Tensor y, torch::Tensor dy, torch::Tensor row_indices_in,
+                                      torch::Tensor row_offsets, torch::Tensor column_indices,
+                                      double scale) {
+  TSP_CHECK_CUDA_F32(y, "y");
+  TSP_CHECK_CUDA_F32(dy, "dy");
+  TORCH_CHECK(y.sizes() == dy.sizes(), "torch_sputnik.sparse_softmax_backward: y and dy must have the same shape");
+  c10::cuda::CUDAGuard guard(y.device());
+  torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
+  const int64_t m = row_indices.size(0);
+  check_topology(m, row_indices, row_offsets, column_indices);
+  const int64_t nnz = column_indices.size(0);
+  TORCH_CHECK(y.size(-1) == nnz, "torch_sputnik.sparse_softmax_backward: bad number of values");
+  const int64_t replicas = y.dim() == 2 ? y.size(0) : 1;
+  torch::Tensor dx = torch::empty_like(y);
+  check_rc(tsp_csr_softmax_backward_f32((int)m, (int)nnz, (int)replicas, (float)scale,
+                                        y.data_ptr<float>(), dy.data_ptr<float>(),
+                                        row_indices.data_ptr<int>(), row_offsets.data_ptr<int>(),
+                                        dx.data_ptr<float>(), current_stream()),
+           "sparse_softmax_backward");
+  return dx;
+}
+
+static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tensor& values,
+                                                 const torch::Tensor& row_offsets,
+                                                 const torch::Tensor& column_indices,
+                                                 bool want_perm) {
+  // The reference handles 1-D values only (src/transpose_cuda.cu:58); its own 3-D backward
+  // passes hand it [R, nnz] (modules/spmm.py:59) and get garbage.  Here [R, nnz] is permuted
+  // replica by replica with the shared topology.
+  TORCH_CHECK(values.dim() == 1 || values.dim() == 2,
+              "torch_sputnik.csr_transpose: values must have 1 or 2 dimensions");
+  TSP_CHECK_CUDA_F32(values, "values");
+  TSP_CHECK_CUDA_I32(row_offsets, "row_offsets");
+  TSP_CHECK_CUDA_I32(column_indices, "column_indices");
+  TORCH_CHECK(row_offsets.dim() == 1 && row_offsets.size(0) == m + 1,
+              "torch_sputnik.csr_transpose: expected m+1 row offsets");
+  TORCH_CHECK(column_indices.dim() == 1, "torch_sputnik.csr_transpose: column_indices must be 1-D");
+  const int64_t nnz = column_indices.size(0);
+  TORCH_CHECK(values.size(-1) == nnz,
+              "torch_sputnik.csr_transpose: expected same number of values and indices");
+  c10::cuda::CUDAGuard guard(values.device());
+  const int64_t replicas = values.dim() == 2 ? values.size(0) : 1;
+
+  auto fopt = torch::TensorOptions().dtype(torch::kFloat32).device(values.device());
+  auto iopt = torch::TensorOptions().dtype(torch::kInt32).device(values.device());
+  torch::Tensor values_t = torch::empty_like(values);
+  torch::Tensor row_offsets_t = torch::empty({n + 1}, iopt);
+  torch::Tensor column_indices_t = torch::empty({nnz}, iopt);
+  torch::Tensor perm;
+  if (want_perm) perm = torch::empty({nnz}, iopt);
+  const size_t ws_bytes = tsp_csr_transpose_workspace(m, n, (int)nnz);
+  torch::Tensor ws = torch::empty({(int64_t)ws_bytes},
+                                  torch::TensorOptions().dtype(torch::kUInt8).device(values.device()));
+  check_rc(tsp_csr_transpose_f32(m, n, (int)nnz, (int)replicas, values.data_ptr<float>(),
+                                 row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                                 values_t.data_ptr<float>(), row_offsets_t.data_ptr<int>(),
+                                 column_indices_t.data_ptr<int>(),
+                                 want_perm ? perm.data_ptr<int>() : nullptr, ws.data_ptr(), ws_bytes,
+                                 current_stream()),
+           "csr_transpose");
+  std::vector<torch::Tensor> out{values_t, row_offsets_t, column_indices_t};
+  if (want_perm) out.push_back(perm);
+  (void)fopt;
+  return out;
+}
+
+// src/sputnik.cpp:30-34 -> src/transpose_cuda.cu:45-102
+std::vector<torch::Tensor> csr_transpose(int m, int n, torch::Tensor values,
+                                         torch::Tensor row_offsets, torch::Tensor column_indices) {
+  return transpose_impl(m, n, values, row_offsets, column_indices, false);
+}
+
+// Extension: also returns perm (values_t = values[..., perm]) so a static topology is sorted once.
+std::vector<torch::Tensor> csr_transpose_with_perm(int m, int n, torch::Tensor values,
+                                                   torch::Tensor row_offsets,
+                                                   torch::Tensor column_indices) {
+  return transpose_impl(m, n, values, row_offsets, column_indices, true);
+}
+
+torch::Tensor permute_values(torch::Tensor values, torch::Tensor perm) {
+  TSP_CHECK_CUDA_F32(values, "values");
+  TSP_CHECK_CUDA_I32(perm, "perm");
+  TORCH_CHECK(values.dim() == 1 || values.dim() == 2, "torch_sputnik.permute_values: values must be 1-D or 2-D");
+  TORCH_CHECK(perm.dim() == 1 && perm.size(0) == values.size(-1),
+              "torch_sputnik.permute_values: perm must have nnz elements");
+  c10::cuda::CUDAGuard guard(values.device());
+  torch::Tensor out = torch::empty_like(values);
+  check_rc(tsp_permute_values_f32((int)perm.size(0), values.dim() == 2 ? (int)values.size(0) : 1,
+                                  values.data_ptr<float>(), perm.data_ptr<int>(),
+                                  out.data_ptr<float>(), current_stream()),
+           "permute_values");
+  return out;
+}
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.doc() = "B200-native CSR sparse kernels behind the torch_sputnik operator API";
+  m.def("spmm", &spmm, "Sparse Matrix Matrix Multiplication: AxB");
+  m.def("left_spmm", &left_spmm, "Sparse Matrix Matrix Multiplication: A(2d)xB(3d)");
+  m.def("sddmm", &sddmm, "Sampled Dense Dense Matrix Multiplication: (AxB).C = D");
+  m.def("sparse_softmax", &sparse_softmax,
+        "Computes softmax function across the last dim of a sparse matrix");
+  m.def("csr_transpose", &csr_transpose, "Transpose sparse matrix");
+  m.def("spmm_bias_relu", &spmm_bias_relu, "relu(AxB + bias[:, None])");
+  m.def("spmm_bias", &spmm_bias_relu, "alias of spmm_bias_relu (tests/test_spmm_bias_relu.py:37)");
+  m.def("sparse_softmax_scaled", &sparse_softmax_scaled, "softmax(scale * x) over CSR rows");
+  m.def("sparse_softmax_backward", &sparse_softmax_backward, "gradient of sparse_softmax_scaled");
+  m.def("csr_transpose_with_perm", &csr_transpose_with_perm, "csr_transpose + permutation");
+  m.def("permute_values", &permute_values, "values[..., perm]");
+  m.def("set_variant", [](const std::string& op, int v) { return tsp_set_variant(op.c_str(), v); },
+        "force a kernel variant (benchmarking only)");
+  m.def("launch_count", []() { return tsp_launch_count(); }, "kernels launched so far");
+  m.def("abi_version", []() { return tsp_version(); });
+}

@@ -1,0 +1,313 @@
+// tsp_abi.cu -- the C-ABI of libtsp.so (declared in include/tsp.h): argument validation,
+// kernel-variant heuristics and launches.  Torch-free; the PyTorch shim (torch_shim.cpp) and
+// any other host (ctypes, a C++ harness) call exactly these symbols.
+#include "../../include/tsp.h"
+
+#include <cstring>
+#include <mutex>
+
+#include "kernels/common.cuh"
+#include "kernels/csr_softmax.cuh"
+#include "kernels/csr_transpose.cuh"
+#include "kernels/sddmm_gather.cuh"
+#include "kernels/spmm_gather.cuh"
+#include "kernels/spmm_staged.cuh"
+#include "kernels/sddmm_staged.cuh"
+
+namespace tsp {
+
+static thread_local char t_error[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+static std::atomic<int> g_spmm_variant{0};
+static std::atomic<int> g_sddmm_variant{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_error, sizeof(t_error), fmt, ap);
+  va_end(ap);
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+      v = 148;
+    cached[dev] = v;
+  }
+  return cached[dev];
+}
+
+static int invalid(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_error, sizeof(t_error), fmt, ap);
+  va_end(ap);
+  return TSP_ERR_INVALID_ARGUMENT;
+}
+
+}  // namespace tsp
+
+using namespace tsp;
+
+extern "C" {
+
+int tsp_version(void) { return TSP_VERSION; }
+
+const char* tsp_last_error(void) { return t_error; }
+
+unsigned long long tsp_launch_count(void) { return g_launches.load(); }
+
+int tsp_set_variant(const char* op, int variant) {
+  if (op && strcmp(op, "spmm") == 0) return g_spmm_variant.exchange(variant);
+  if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
+  return -1;
+}
+
+// ------------------------------------------------------------------------------------ SpMM
+int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
+                 const int* row_indices, const float* values, const int* row_offsets,
+                 const int* column_indices, const float* dense, const float* bias_or_null,
+                 int relu, float* out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_spmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k, n,
+                   nnz, replicas);
+  if (replicas > 65535) return invalid("tsp_spmm_f32: replicas=%d exceeds 65535", replicas);
+  if (m == 0 || n == 0 || replicas == 0) return TSP_OK;
+  if (!row_offsets || !out || (nnz > 0 && (!values || !column_indices || !dense)))
+    return invalid("tsp_spmm_f32: null pointer argument");
+
+  SpmmArgs a;
+  a.m = m; a.k = k; a.n = n; a.nnz = nnz;
+  a.values_stride = values_shared ? 0 : (long long)nnz;
+  a.row_indices = row_indices;
+  a.values = values;
+  a.row_offsets = row_offsets;
+  a.column_indices = column_indices;
+  a.dense = dense;
+  a.bias = bias_or_null;
+  a.relu = relu;
+  a.out = out;
+
+  const int variant = g_spmm_variant.load();
+  const bool vec4_ok = (n % 4 == 0) && aligned16(dense) && aligned16(out);
+  const bool vec2_ok = (n % 2 == 0) && ((reinterpret_cast<uintptr_t>(dense) & 7u) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(out) & 7u) == 0);
+
+  if (variant != 1 && spmm_staged_applicable(a, replicas)) {
+    const int rc = launch_spmm_staged(a, replicas, stream);
+    if (rc >= 0) return rc;  // < 0: staged path declined, use the gather kernel
+  }
+
+  if (vec4_ok && n > 128) {
+    launch_spmm_gather<4, 2>(a, replicas, stream);
+  } else if (vec4_ok && n > 64) {
+    launch_spmm_gather<4, 1>(a, replicas, stream);
+  } else if (vec2_ok && n > 64) {
+    launch_spmm_gather<2, 2>(a, replicas, stream);
+  } else if (vec2_ok && n > 32) {
+    launch_spmm_gather<2, 1>(a, replicas, stream);
+  } else if (n > 32) {
+    launch_spmm_gather<1, 2>(a, replicas, stream);
+  } else {
+    launch_spmm_gather<1, 1>(a, replicas, stream);
+  }
+  TSP_CHECK_LAUNCH("tsp_spmm_f32 (gather)");
+  return TSP_OK;
+}
+
+// ----------------------------------------------------------------------------------- SDDMM
+int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                  const int* row_offsets, const int* column_indices, const float* lhs,
+                  const float* rhs, float* out, void* stream_) {
+  (void)row_indices;  // the flat-nonzero decomposition is balanced without a row swizzle
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_sddmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k,
+                   n, nnz, replicas);
+  if (replicas > 65535) return invalid("tsp_sddmm_f32: replicas=%d exceeds 65535", replicas);
+  if (nnz == 0 || replicas == 0) return TSP_OK;
+  if (!row_offsets || !column_indices || !out || (k > 0 && (!lhs || !rhs)))
+    return invalid("tsp_sddmm_f32: null pointer argument");
+
+  SddmmArgs a;
+  a.m = m; a.k = k; a.n = n; a.nnz = nnz;
+  a.row_offsets = row_offsets;
+  a.column_indices = column_indices;
+  a.lhs = lhs;
+  a.rhs = rhs;
+  a.out = out;
+
+  const int variant = g_sddmm_variant.load();
+  if (variant != 1 && sddmm_staged_applicable(a, replicas)) {
+    const int rc = launch_sddmm_staged(a, replicas, stream);
+    if (rc >= 0) return rc;
+  }
+
+  const bool vec4_ok = (k % 4 == 0) && aligned16(lhs) && aligned16(rhs);
+  if (vec4_ok) {
+    if (k <= 32) launch_sddmm_gather<4, 8>(a, replicas, stream);
+    else if (k <= 64) launch_sddmm_gather<4, 16>(a, replicas, stream);
+    else launch_sddmm_gather<4, 32>(a, replicas, stream);
+  } else {
+    if (k <= 8) launch_sddmm_gather<1, 8>(a, replicas, stream);
+    else if (k <= 16) launch_sddmm_gather<1, 16>(a, replicas, stream);
+    else launch_sddmm_gather<1, 32>(a, replicas, stream);
+  }
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (gather)");
+  return TSP_OK;
+}
+
+// --------------------------------------------------------------------------------- softmax
+static int pick_softmax_reg(int m, int nnz) {
+  const long long avg = m > 0 ? (long long)nnz / m : 0;
+  const long long want = avg + avg / 4 + 32;
+  if (want <= 32 * 4) return 4;
+  if (want <= 32 * 8) return 8;
+  if (want <= 32 * 16) return 16;
+  return 32;
+}
+
+int tsp_csr_softmax_f32(int m, int nnz, int replicas, float scale, const float* values,
+                        const int* row_indices, const int* row_offsets, float* out,
+                        void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || nnz < 0 || replicas < 0) return invalid("tsp_csr_softmax_f32: negative dimension");
+  if (replicas > 65535) return invalid("tsp_csr_softmax_f32: replicas=%d exceeds 65535", replicas);
+  if (m == 0 || nnz == 0 || replicas == 0) return TSP_OK;
+  if (!values || !row_offsets || !out) return invalid("tsp_csr_softmax_f32: null pointer argument");
+  SoftmaxArgs a;
+  a.m = m; a.nnz = nnz; a.scale = scale;
+  a.row_indices = row_indices;
+  a.row_offsets = row_offsets;
+  a.x = values; a.dy = nullptr; a.out = out;
+  constexpr int WARPS = 8;
+  dim3 grid(ceil_div(m, WARPS), replicas);
+  switch (pick_softmax_reg(m, nnz)) {
+    case 4: csr_softmax_kernel<4, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 8: csr_softmax_kernel<8, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 16: csr_softmax_kernel<16, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    default: csr_softmax_kernel<32, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+  }
+  TSP_CHECK_LAUNCH("tsp_csr_softmax_f32");
+  return TSP_OK;
+}
+
+int tsp_csr_softmax_backward_f32(int m, int nnz, int replicas, float scale, const float* y,
+                                 const float* dy, const int* row_indices, const int* row_offsets,
+                                 float* dx, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_csr_softmax_backward_f32: negative dimension");
+  if (replicas > 65535)
+    return invalid("tsp_csr_softmax_backward_f32: replicas=%d exceeds 65535", replicas);
+  if (m == 0 || nnz == 0 || replicas == 0) return TSP_OK;
+  if (!y || !dy || !row_offsets || !dx)
+    return invalid("tsp_csr_softmax_backward_f32: null pointer argument");
+  SoftmaxArgs a;
+  a.m = m; a.nnz = nnz; a.scale = scale;
+  a.row_indices = row_indices;
+  a.row_offsets = row_offsets;
+  a.x = y; a.dy = dy; a.out = dx;
+  constexpr int WARPS = 8;
+  dim3 grid(ceil_div(m, WARPS), replicas);
+  switch (pick_softmax_reg(m, nnz)) {
+    case 4: csr_softmax_bwd_kernel<4, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 8: csr_softmax_bwd_kernel<8, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    default: csr_softmax_bwd_kernel<16, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+  }
+  TSP_CHECK_LAUNCH("tsp_csr_softmax_backward_f32");
+  return TSP_OK;
+}
+
+// ------------------------------------------------------------------------------- transpose
+static size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+size_t tsp_csr_transpose_workspace(int m, int n, int nnz) {
+  (void)m;
+  if (nnz < 0 || n < 0) return 0;
+  const SortPlan p = make_sort_plan(n, nnz);
+  // keys A/B, payload A/B, [radix][tiles] histogram
+  return 4 * align256(sizeof(int) * (size_t)nnz) + align256(sizeof(int) * (size_t)p.radix * p.tiles) +
+         256;
+}
+
+int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* values,
+                          const int* row_offsets, const int* column_indices, float* values_t,
+                          int* row_offsets_t, int* column_indices_t, int* perm_or_null,
+                          void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_csr_transpose_f32: negative dimension");
+  if (!row_offsets_t) return invalid("tsp_csr_transpose_f32: null row_offsets_t");
+  if (nnz > 0 && (!values || !row_offsets || !column_indices || !values_t || !column_indices_t))
+    return invalid("tsp_csr_transpose_f32: null pointer argument");
+  if (nnz == 0) {
+    fill_int_kernel<<<ceil_div(n + 1, 256), 256, 0, stream>>>(row_offsets_t, n + 1, 0);
+    TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (empty)");
+    return TSP_OK;
+  }
+  if (workspace_bytes < tsp_csr_transpose_workspace(m, n, nnz) || !workspace) {
+    set_error("tsp_csr_transpose_f32: workspace of %zu bytes is smaller than the %zu required",
+              workspace_bytes, tsp_csr_transpose_workspace(m, n, nnz));
+    return TSP_ERR_WORKSPACE;
+  }
+  if ((reinterpret_cast<uintptr_t>(workspace) & 255u) != 0)
+    return invalid("tsp_csr_transpose_f32: workspace must be 256-byte aligned");
+
+  const SortPlan p = make_sort_plan(n, nnz);
+  char* ws = static_cast<char*>(workspace);
+  const size_t seg = align256(sizeof(int) * (size_t)nnz);
+  int* keys[2] = {reinterpret_cast<int*>(ws), reinterpret_cast<int*>(ws + seg)};
+  int* pay[2] = {reinterpret_cast<int*>(ws + 2 * seg), reinterpret_cast<int*>(ws + 3 * seg)};
+  int* hist = reinterpret_cast<int*>(ws + 4 * seg);
+
+  const int* kin = column_indices;
+  const int* pin = nullptr;
+  for (int pass = 0; pass < p.passes; ++pass) {
+    const int shift = pass * p.digit_bits;
+    radix_hist_kernel<<<p.tiles, kSortThreads, 0, stream>>>(kin, nnz, shift, p.radix, p.tiles, hist);
+    TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (hist)");
+    exclusive_scan_kernel<<<1, 1024, 0, stream>>>(hist, p.radix * p.tiles);
+    TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (scan)");
+    radix_scatter_kernel<<<p.tiles, kSortThreads, 0, stream>>>(kin, pin, nnz, shift, p.radix,
+                                                              p.tiles, hist, keys[pass & 1],
+                                                              pay[pass & 1]);
+    TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (scatter)");
+    kin = keys[pass & 1];
+    pin = pay[pass & 1];
+  }
+
+  TransposeFinishArgs f;
+  f.m = m; f.n = n; f.nnz = nnz; f.replicas = replicas;
+  f.sorted_cols = kin;
+  f.sorted_src = pin;
+  f.row_offsets = row_offsets;
+  f.values = values;
+  f.values_t = values_t;
+  f.row_offsets_t = row_offsets_t;
+  f.column_indices_t = column_indices_t;
+  f.perm = perm_or_null;
+  transpose_finish_kernel<<<ceil_div((long long)nnz + 1, 256), 256, 0, stream>>>(f);
+  TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (finish)");
+  return TSP_OK;
+}
+
+int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int* perm,
+                           float* values_t, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (nnz < 0 || replicas < 0) return invalid("tsp_permute_values_f32: negative dimension");
+  if (replicas > 65535) return invalid("tsp_permute_values_f32: replicas=%d exceeds 65535", replicas);
+  if (nnz == 0 || replicas == 0) return TSP_OK;
+  if (!values || !perm || !values_t) return invalid("tsp_permute_values_f32: null pointer argument");
+  dim3 grid(ceil_div(nnz, 256), replicas);
+  permute_values_kernel<<<grid, 256, 0, stream>>>(nnz, values, perm, values_t);
+  TSP_CHECK_LAUNCH("tsp_permute_values_f32");
+  return TSP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,171 @@
+"""Autograd layer over the ``torch_sputnik`` ops -- the host-side mirror of the reference's
+``modules/`` package (same class names, argument order and meaning), written against the
+B200 extension.
+
+Differences from the reference, all on purpose:
+
+* ``Spmm`` / ``Sddmm`` backward work for replicated (3-D) operands: the reference hands
+  ``[R, nnz]`` values to a ``csr_transpose`` that only understands ``[nnz]``
+  (modules/spmm.py:59, src/transpose_cuda.cu:58).
+* the transpose of a static topology is computed once per (row_offsets, column_indices) pair
+  and cached as a permutation (``TransposedTopology``); later backward passes only gather.
+* ``CsrSoftmax`` is a real autograd Function (the reference calls the op directly and gets no
+  gradient, modules/sparse_attention.py:76) and folds the ``1/sqrt(d)`` scale.
+* ``diffsort`` returns int32 heaviest-row-first; the reference's expression sorts lightest
+  first.  Results never depend on the swizzle.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import torch_sputnik as ops
+
+
+def diffsort(offsets: torch.Tensor) -> torch.Tensor:
+    """Row swizzle from row offsets: rows ordered by decreasing nonzero count (int32)."""
+    lens = offsets[1:] - offsets[:-1]
+    return torch.argsort(lens, descending=True, stable=True).to(torch.int32)
+
+
+def dense_to_sparse(matrix: torch.Tensor):
+    """(values, row_indices, row_offsets, column_indices) of a dense 2-D tensor -- the contract
+    of modules/sparse_linear.py:9-16 (float32 values, int32 indices)."""
+    csr = matrix.detach().to_sparse_csr()
+    values = csr.values().clone().to(torch.float32)
+    row_offsets = csr.crow_indices().to(torch.int32).contiguous()
+    column_indices = csr.col_indices().to(torch.int32).contiguous()
+    return values, diffsort(row_offsets), row_offsets, column_indices
+
+
+class TransposedTopology:
+    """CSC view of a static CSR topology: (row_offsets_t, column_indices_t, row_indices_t, perm)."""
+
+    def __init__(self, m, n, row_offsets, column_indices):
+        probe = torch.empty(column_indices.shape[0], dtype=torch.float32, device=column_indices.device)
+        _, self.row_offsets, self.column_indices, self.perm = ops.csr_transpose_with_perm(
+            m, n, probe, row_offsets, column_indices)
+        self.row_indices = diffsort(self.row_offsets)
+
+    @classmethod
+    def get(cls, m, n, row_offsets, column_indices) -> "TransposedTopology":
+        """Cached on the row_offsets tensor itself, so it lives exactly as long as the topology;
+        keyed on the partner tensor and both version counters (in-place edits invalidate)."""
+        store = row_offsets.__dict__.setdefault("_tsp_transposed", {})
+        key = (m, n, column_indices.data_ptr(), column_indices.shape[0], row_offsets._version,
+               column_indices._version)
+        hit = store.get(key)
+        if hit is None:
+            store.clear()
+            hit = store[key] = cls(m, n, row_offsets, column_indices)
+        return hit
+
+
+class Spmm(torch.autograd.Function):
+    """out = CSR(values) @ dense.  Arguments as modules/spmm.py:26-36."""
+
+    @staticmethod
+    def forward(ctx, m, k, values, row_indices, row_offsets, column_indices, dense):
+        ctx.m, ctx.k = m, k
+        ctx.topology = (row_indices, row_offsets, column_indices)
+        ctx.save_for_backward(values, dense)
+        return ops.spmm(m, k, values, row_indices, row_offsets, column_indices, dense)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        m, k = ctx.m, ctx.k
+        row_indices, row_offsets, column_indices = ctx.topology
+        values, dense = ctx.saved_tensors
+        grad_output = grad_output.contiguous()
+        grad_values = grad_dense = None
+        if ctx.needs_input_grad[2]:
+            # dA = (dC @ B^T) sampled at the pattern; sddmm wants the right operand as [k, n].
+            grad_values = ops.sddmm(m, k, row_indices, row_offsets, column_indices, grad_output,
+                                    dense.contiguous())
+            if values.dim() == 1 and grad_values.dim() == 2:
+                grad_values = grad_values.sum(0)
+        if ctx.needs_input_grad[6]:
+            t = TransposedTopology.get(m, k, row_offsets, column_indices)
+            values_t = ops.permute_values(values.contiguous(), t.perm)
+            grad_dense = ops.spmm(k, m, values_t, t.row_indices, t.row_offsets, t.column_indices,
+                                  grad_output)
+            grad_dense = grad_dense.reshape(dense.shape)
+        return None, None, grad_values, None, None, None, grad_dense
+
+
+class Sddmm(torch.autograd.Function):
+    """out[j] = <lhs[row(j)], rhs[col(j)]>.  Arguments as modules/sddmm.py:26-37."""
+
+    @staticmethod
+    def forward(ctx, m, n, row_indices, row_offsets, column_indices, lhs_matrix, rhs_matrix):
+        ctx.m, ctx.n = m, n
+        ctx.topology = (row_indices, row_offsets, column_indices)
+        ctx.save_for_backward(lhs_matrix, rhs_matrix)
+        return ops.sddmm(m, n, row_indices, row_offsets, column_indices, lhs_matrix, rhs_matrix)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        m, n = ctx.m, ctx.n
+        row_indices, row_offsets, column_indices = ctx.topology
+        lhs, rhs = ctx.saved_tensors
+        grad_output = grad_output.contiguous()
+        grad_lhs = grad_rhs = None
+        if ctx.needs_input_grad[5]:
+            grad_lhs = ops.spmm(m, n, grad_output, row_indices, row_offsets, column_indices,
+                                rhs.contiguous()).reshape(lhs.shape)
+        if ctx.needs_input_grad[6]:
+            t = TransposedTopology.get(m, n, row_offsets, column_indices)
+            grad_t = ops.permute_values(grad_output, t.perm)
+            grad_rhs = ops.spmm(n, m, grad_t, t.row_indices, t.row_offsets, t.column_indices,
+                                lhs.contiguous()).reshape(rhs.shape)
+        return None, None, None, None, None, grad_lhs, grad_rhs
+
+
+class CsrSoftmax(torch.autograd.Function):
+    """Row softmax over CSR values with a fused pre-scale: softmax(scale * x)."""
+
+    @staticmethod
+    def forward(ctx, values, row_indices, row_offsets, column_indices, scale=1.0):
+        y = ops.sparse_softmax_scaled(values.contiguous(), row_indices, row_offsets, column_indices,
+                                      float(scale))
+        ctx.topology = (row_indices, row_offsets, column_indices)
+        ctx.scale = float(scale)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        (y,) = ctx.saved_tensors
+        row_indices, row_offsets, column_indices = ctx.topology
+        dx = ops.sparse_softmax_backward(y, grad_output.contiguous(), row_indices, row_offsets,
+                                         column_indices, ctx.scale)
+        return dx, None, None, None, None
+
+
+class SparseLinearFunction(torch.autograd.Function):
+    """out[b] = W_csr @ dense[b] with one weight for every batch entry (``left_spmm``).
+    Arguments as modules/sparse_linear.py:19-30; ``dense`` is [B, in_features, tokens]."""
+
+    @staticmethod
+    def forward(ctx, m, k, values, row_indices, row_offsets, column_indices, dense):
+        ctx.m, ctx.k = m, k
+        ctx.topology = (row_indices, row_offsets, column_indices)
+        ctx.save_for_backward(values, dense)
+        return ops.left_spmm(m, k, values, row_indices, row_offsets, column_indices, dense)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        m, k = ctx.m, ctx.k
+        row_indices, row_offsets, column_indices = ctx.topology
+        values, dense = ctx.saved_tensors
+        grad_output = grad_output.contiguous()
+        grad_values = grad_dense = None
+        if ctx.needs_input_grad[2]:
+            gv = ops.sddmm(m, k, row_indices, row_offsets, column_indices, grad_output,
+                           dense.contiguous())
+            grad_values = gv.sum(0) if gv.dim() == 2 else gv
+        if ctx.needs_input_grad[6]:
+            t = TransposedTopology.get(m, k, row_offsets, column_indices)
+            values_t = ops.permute_values(values.contiguous(), t.perm)
+            grad_dense = ops.left_spmm(k, m, values_t, t.row_indices, t.row_offsets,
+                                       t.column_indices, grad_output).reshape(dense.shape)
+        return None, None, grad_values, None, None, None, grad_dense
