@@ -122,7 +122,7 @@ def test_sparse_attention_module_forward_backward_runs(dev):
     att.prune_and_setup(seed=0)
     x = torch.randn(2, 64, 128, device=dev, requires_grad=True)
     y = att(x, x, x)
-    assert tuple(y.shape) == (2, 128, 64)
+    assert tuple(y.shape) == (2, 64, 128)
     y.square().mean().backward()
     assert x.grad is not None and torch.isfinite(x.grad).all()
     for lin in att.linears:
