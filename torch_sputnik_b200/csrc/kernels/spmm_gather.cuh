@@ -28,7 +28,15 @@ struct SpmmArgs {
   const float* bias;  // may be null
   int relu;
   float* out;
+  // When guard_id != 0 the gather kernel is the fallback of a staged launch: it runs only if the
+  // sorted-columns check raised g_unsorted_flag[guard_slot] == guard_id.
+  int guard_slot = 0;
+  unsigned guard_id = 0;
 };
+
+// Per-call "columns are not sorted" flags, written by csr_check_sorted_kernel (spmm_staged.cuh).
+constexpr int kFlagSlots = 1024;
+__device__ unsigned g_unsorted_flag[kFlagSlots];
 
 template <int VEC>
 struct VecT;
@@ -72,6 +80,7 @@ __device__ __forceinline__ void store_vec(float* p, const float (&src)[VEC]) {
 template <int VEC, int U, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs a) {
   __shared__ __align__(16) int2 s_pairs[WARPS][32];
+  if (a.guard_id != 0 && g_unsorted_flag[a.guard_slot] != a.guard_id) return;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;

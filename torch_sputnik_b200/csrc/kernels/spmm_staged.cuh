@@ -1,7 +1,321 @@
-// spmm_staged.cuh -- placeholder until the staged SpMM kernel lands.
+// spmm_staged.cuh -- CSR SpMM, variant 2 ("staged"): the fast path for sorted-column CSR.
+//
+// Why a second kernel.  A pure gather SpMM (the reference's design, cuda_spmm.cu.cc:224-238, and
+// our variant 1) needs 4 bytes of L1/shared bandwidth per FMA: one LDG/LDS.128 of the dense
+// operand feeds 4 FFMA.  An SM delivers 128 B/clk of L1/shared and issues 128 FMA/clk, so that
+// design tops out at 25 % of the fp32 peak -- and lower still when the gathers miss L1 and go to
+// L2 (about 42 B/clk/SM).  This kernel attacks both limits:
+//
+//  * the dense operand is STAGED: a dedicated producer warp streams [32 x NT] slabs of B into a
+//    multi-stage shared-memory ring with bulk async copies (cp.async.bulk -> mbarrier
+//    complete_tx, the TMA engine without a descriptor), so every B byte crosses L2->SM once per
+//    row block, coalesced, and all gathers hit shared memory;
+//  * rows are MERGED four at a time: the four rows' nonzeros that fall in the slab are scattered
+//    into a dense [32 x 4] value tile (zeros elsewhere) plus a 32-bit occupancy mask; the warp
+//    then walks the set bits, and for every occupied column loads the B row segment ONCE
+//    (LDS.128 per lane) and one broadcast LDS.128 of the four values, and issues 4 x NT/32 FMAs.
+//    That raises FMA per shared-memory wavefront from 1 : 1 (gather) to about R*d/(1-(1-d)^R)
+//    useful FMAs per B load, R = 4: x1.16 at d = 0.1, x2.1 at d = 0.5 (DESIGN.md has the table);
+//  * the FMA stream is packed fma.rn.f32x2 (SASS FFMA2): half the issue slots for the same
+//    arithmetic and rounding, leaving issue room for the LDS and the bit-walk.
+//
+// Arithmetic: per output element, fp32 FMAs in ascending column order, exactly the reference's
+// order; entries a row does not have contribute fma(0, b, acc) = acc for finite b.
+// Precondition: column indices strictly ascending inside each row (what to_sparse_csr and the
+// reference's generators produce).  tsp_spmm_f32 verifies it on the device in the same stream
+// (csr_check_sorted_kernel) and falls back to the gather kernel if it does not hold.
 #pragma once
 #include "spmm_gather.cuh"
+
 namespace tsp {
-inline bool spmm_staged_applicable(const SpmmArgs&, int) { return false; }
-inline int launch_spmm_staged(const SpmmArgs&, int, cudaStream_t) { return -1; }
+
+// flag[slot] = call_id if some row has a column index not greater than its predecessor.
+__global__ void __launch_bounds__(256)
+csr_check_sorted_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m,
+                        int slot, unsigned call_id) {
+  const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * 256) >> 5;
+  bool bad = false;
+  for (int row = warp; row < m; row += nwarps) {
+    const int beg = __ldg(row_offsets + row), end = __ldg(row_offsets + row + 1);
+    for (int j = beg + lane; j + 1 < end; j += 32) bad |= __ldg(cols + j) >= __ldg(cols + j + 1);
+  }
+  if (__any_sync(kFullMask, bad) && lane == 0) g_unsorted_flag[slot] = call_id;
+}
+
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void fma2(unsigned long long& d, unsigned long long a,
+                                     unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
+}
+
+template <int NV4_, int G_, int STAGES_, int WARPS_, int U_>
+struct StagedCfg {
+  static constexpr int NV4 = NV4_;        // float4 chunks of B per lane
+  static constexpr int NT = 128 * NV4_;   // output columns per CTA
+  static constexpr int G = G_;            // 4-row groups per warp
+  static constexpr int KS = 32;           // slab depth == width of the occupancy mask
+  static constexpr int STAGES = STAGES_;
+  static constexpr int WARPS = WARPS_;    // compute warps (+1 producer warp)
+  static constexpr int U = U_;            // prefetched candidates per row per slab = 8*U
+  static constexpr int RB = WARPS_ * G_ * 4;  // rows per CTA
+  static constexpr int THREADS = (WARPS_ + 1) * 32;
+  static constexpr size_t kSlabFloats = (size_t)KS * NT;
+  static constexpr size_t kSmemBytes =
+      sizeof(float) * (STAGES_ * kSlabFloats + (size_t)WARPS_ * G_ * KS * 4) + 2 * STAGES_ * 8 + 128;
+};
+
+struct StagedGuard {
+  int slot;          // index into g_unsorted_flag
+  unsigned call_id;  // this call's id; flag == call_id  <=>  columns are not sorted
+};
+
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::THREADS, (Cfg::kSmemBytes <= 110 * 1024) ? 2 : 1)
+spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
+  constexpr int NV4 = Cfg::NV4, NT = Cfg::NT, G = Cfg::G, KS = Cfg::KS, STAGES = Cfg::STAGES,
+                WARPS = Cfg::WARPS, U = Cfg::U;
+  if (g_unsorted_flag[guard.slot] == guard.call_id) return;  // gather kernel takes over
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* const b_ring = reinterpret_cast<float*>(smem_raw);
+  float* const a_tiles = b_ring + STAGES * Cfg::kSlabFloats;
+  unsigned long long* const full = reinterpret_cast<unsigned long long*>(a_tiles + WARPS * G * KS * 4);
+  unsigned long long* const empty = full + STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = a.n, k = a.k;
+  const int n0 = blockIdx.y * NT;
+  const int rep = blockIdx.z;
+  const int nslabs = (k + KS - 1) / KS;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, WARPS);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == WARPS) {
+    // ---------------- producer warp: stream B slabs into the ring ----------------
+    const float* __restrict__ dense = a.dense + (size_t)rep * k * n + n0;
+    const unsigned row_bytes = (unsigned)min(NT, n - n0) * 4u;
+    for (int s = 0; s < nslabs; ++s) {
+      const int st = s % STAGES, use = s / STAGES;
+      if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
+      const int rows = min(KS, k - s * KS);
+      if (lane == 0) mbar_arrive_expect_tx(full + st, rows * row_bytes);
+      __syncwarp();
+      if (lane < rows)
+        bulk_g2s(b_ring + st * Cfg::kSlabFloats + lane * NT, dense + (size_t)(s * KS + lane) * n,
+                 row_bytes, full + st);
+    }
+    return;
+  }
+
+  // ---------------- compute warps ----------------
+  const int r_lane = lane >> 3, t_lane = lane & 7;  // lane <-> (row in group, candidate slot)
+  const float* __restrict__ vals = a.values + (size_t)rep * a.values_stride;
+  const int* __restrict__ cols = a.column_indices;
+  float* const at = a_tiles + warp * (G * KS * 4);
+
+  int pos[G], endp[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const int item = blockIdx.x * Cfg::RB + (warp * G + g) * 4 + r_lane;
+    pos[g] = endp[g] = 0;
+    if (item < a.m) {
+      const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
+      pos[g] = __ldg(a.row_offsets + row);
+      endp[g] = __ldg(a.row_offsets + row + 1);
+    }
+  }
+
+  unsigned long long acc[G][4][NV4 * 2];
+#pragma unroll
+  for (int g = 0; g < G; ++g)
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int j = 0; j < NV4 * 2; ++j) acc[g][r][j] = 0ull;
+
+  // Candidates for the next slab: up to 8*U entries per row starting at the row cursor.
+  int pc[G][U];
+  float pv[G][U];
+  auto prefetch = [&]() {
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int idx = pos[g] + u * 8 + t_lane;
+        const bool in = idx < endp[g];
+        pc[g][u] = in ? __ldg(cols + idx) : 0x7fffffff;
+        pv[g][u] = in ? __ldg(vals + idx) : 0.f;
+      }
+  };
+  prefetch();
+
+  for (int s = 0; s < nslabs; ++s) {
+    const int st = s % STAGES, use = s / STAGES;
+    const int k0 = s * KS, k1 = k0 + KS;
+    unsigned masks[G];
+
+    // -- build the [KS x 4] value tiles of this slab from the prefetched candidates
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+      reinterpret_cast<float4*>(at + g * KS * 4)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      unsigned bits = 0;
+      int taken = 0;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const bool take = pc[g][u] < k1;
+        if (take) {
+          at[(g * KS + (pc[g][u] - k0)) * 4 + r_lane] = pv[g][u];
+          bits |= 1u << (pc[g][u] - k0);
+        }
+        taken += __popc(__ballot_sync(kFullMask, take) & (0xffu << (r_lane * 8)));
+      }
+      pos[g] += taken;
+      // Rare: a row has more than 8*U entries in this slab -- keep consuming synchronously.
+      bool full_batch = taken == 8 * U;
+      while (__any_sync(kFullMask, full_batch)) {
+        const int idx = pos[g] + t_lane;
+        const bool in = full_batch && idx < endp[g];
+        const int c = in ? __ldg(cols + idx) : 0x7fffffff;
+        const bool take = c < k1;
+        if (take) {
+          at[(g * KS + (c - k0)) * 4 + r_lane] = __ldg(vals + idx);
+          bits |= 1u << (c - k0);
+        }
+        const int got = __popc(__ballot_sync(kFullMask, take) & (0xffu << (r_lane * 8)));
+        pos[g] += got;
+        full_batch = got == 8;
+      }
+      masks[g] = __reduce_or_sync(kFullMask, bits);
+    }
+    __syncwarp();
+    prefetch();  // for slab s+1; the loads fly under the FMA loop below
+
+    mbar_wait(full + st, use & 1);
+    const float* const bs = b_ring + st * Cfg::kSlabFloats + lane * 4;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      unsigned mk = masks[g];
+      const float* const ag = at + g * KS * 4;
+      while (mk) {
+        const int kk = __ffs(mk) - 1;
+        mk &= mk - 1;
+        const float4 av = *reinterpret_cast<const float4*>(ag + kk * 4);
+        ulonglong2 bv[NV4];
+#pragma unroll
+        for (int j = 0; j < NV4; ++j)
+          bv[j] = *reinterpret_cast<const ulonglong2*>(bs + kk * NT + j * 128);
+        const unsigned long long a2[4] = {pack2(av.x, av.x), pack2(av.y, av.y), pack2(av.z, av.z),
+                                          pack2(av.w, av.w)};
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (int j = 0; j < NV4; ++j) {
+            fma2(acc[g][r][2 * j], a2[r], bv[j].x);
+            fma2(acc[g][r][2 * j + 1], a2[r], bv[j].y);
+          }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + st);
+  }
+
+  // ---------------- epilogue: bias, ReLU, coalesced float4 stores ----------------
+#pragma unroll
+  for (int g = 0; g < G; ++g)
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int item = blockIdx.x * Cfg::RB + (warp * G + g) * 4 + r;
+      if (item >= a.m) continue;
+      const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
+      const float bias = a.bias ? __ldg(a.bias + row) : 0.f;
+      float* __restrict__ out = a.out + ((size_t)rep * a.m + row) * n + n0 + lane * 4;
+#pragma unroll
+      for (int j = 0; j < NV4; ++j) {
+        if (n0 + lane * 4 + j * 128 >= n) continue;
+        float4 o;
+        unpack2(acc[g][r][2 * j], o.x, o.y);
+        unpack2(acc[g][r][2 * j + 1], o.z, o.w);
+        o.x += bias; o.y += bias; o.z += bias; o.w += bias;
+        if (a.relu) {
+          o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+        }
+        *reinterpret_cast<float4*>(out + j * 128) = o;
+      }
+    }
+}
+
+// ------------------------------------------------------------------------------------ host
+inline bool spmm_staged_applicable(const SpmmArgs& a, int replicas) {
+  if (a.n % 4 != 0 || a.n < 96) return false;
+  if (!aligned16(a.dense) || !aligned16(a.out)) return false;
+  if (a.k < 64 || a.nnz == 0) return false;
+  // Small problems are launch-bound; staging cannot pay for its prologue there.
+  return 2.0 * a.nnz * a.n * replicas >= 5.0e7;
+}
+
+template <class Cfg>
+inline int launch_spmm_staged_cfg(const SpmmArgs& a, int replicas, const StagedGuard& guard,
+                                  cudaStream_t stream) {
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(spmm_staged_kernel<Cfg>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)Cfg::kSmemBytes);
+    if (e != cudaSuccess) return cuda_fail(e, "tsp_spmm_f32 (staged smem attribute)");
+    configured[dev] = true;
+  }
+  dim3 grid(ceil_div(a.m, Cfg::RB), ceil_div(a.n, Cfg::NT), replicas);
+  spmm_staged_kernel<Cfg><<<grid, Cfg::THREADS, Cfg::kSmemBytes, stream>>>(a, guard);
+  return 0;
+}
+
+static std::atomic<unsigned> g_call_counter{0};
+
+// Returns TSP_OK / an error code, or -1 if the staged path declines (caller uses gather).
+inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stream) {
+  unsigned id = g_call_counter.fetch_add(1) + 1;
+  if (id == 0) id = g_call_counter.fetch_add(1) + 1;
+  StagedGuard guard{(int)(id % kFlagSlots), id};
+
+  csr_check_sorted_kernel<<<min(ceil_div(a.m, 8), 4 * sm_count()), 256, 0, stream>>>(
+      a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
+  TSP_CHECK_LAUNCH("tsp_spmm_f32 (sorted check)");
+
+  int rc;
+  if (a.n > 128) rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 8, 2>>(a, replicas, guard, stream);
+  else rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 2>>(a, replicas, guard, stream);
+  if (rc != 0) return rc;
+  TSP_CHECK_LAUNCH("tsp_spmm_f32 (staged)");
+
+  // Fallback for unsorted columns: same arguments through the gather kernel, which exits at once
+  // unless the check kernel raised this call's flag.
+  SpmmArgs f = a;
+  f.guard_slot = guard.slot;
+  f.guard_id = guard.call_id;
+  launch_spmm_gather<4, 2>(f, replicas, stream);
+  TSP_CHECK_LAUNCH("tsp_spmm_f32 (gather fallback)");
+  return 0;
+}
+
 }  // namespace tsp
