@@ -68,8 +68,9 @@ struct StagedCfg {
   static constexpr int RB = WARPS_ * G_ * 4;  // rows per CTA
   static constexpr int THREADS = (WARPS_ + 1) * 32;
   static constexpr size_t kSlabFloats = (size_t)KS * NT;
+  static constexpr int kTileFloats = KS * 4 + KS;
   static constexpr size_t kSmemBytes =
-      sizeof(float) * (STAGES_ * kSlabFloats + (size_t)WARPS_ * G_ * KS * 4) + 2 * STAGES_ * 8 + 128;
+      sizeof(float) * (STAGES_ * kSlabFloats + (size_t)WARPS_ * G_ * kTileFloats) + 2 * STAGES_ * 8 + 128;
 };
 
 struct StagedGuard {
@@ -87,7 +88,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* const b_ring = reinterpret_cast<float*>(smem_raw);
   float* const a_tiles = b_ring + STAGES * Cfg::kSlabFloats;
-  unsigned long long* const full = reinterpret_cast<unsigned long long*>(a_tiles + WARPS * G * KS * 4);
+  unsigned long long* const full = reinterpret_cast<unsigned long long*>(a_tiles + WARPS * G * Cfg::kTileFloats);
   unsigned long long* const empty = full + STAGES;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -127,7 +128,8 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   const int r_lane = lane >> 3, t_lane = lane & 7;  // lane <-> (row in group, candidate slot)
   const float* __restrict__ vals = a.values + (size_t)rep * a.values_stride;
   const int* __restrict__ cols = a.column_indices;
-  float* const at = a_tiles + warp * (G * KS * 4);
+  constexpr int kTile = Cfg::kTileFloats;  // KS x 4 values + KS column offsets per 4-row group
+  float* const at = a_tiles + warp * (G * kTile);
 
   int pos[G], endp[G];
 #pragma unroll
@@ -168,61 +170,90 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   for (int s = 0; s < nslabs; ++s) {
     const int st = s % STAGES, use = s / STAGES;
     const int k0 = s * KS, k1 = k0 + KS;
-    unsigned masks[G];
+    int cnts[G];
 
-    // -- build the [KS x 4] value tiles of this slab from the prefetched candidates
+    // -- build this slab's COMPACT tiles from the prefetched candidates: entry i of a group holds
+    //    the four rows' values at the group's i-th occupied column, klist[i] that column's byte
+    //    offset into the B slab.
 #pragma unroll
     for (int g = 0; g < G; ++g)
-      reinterpret_cast<float4*>(at + g * KS * 4)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+      reinterpret_cast<float4*>(at + g * kTile)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
 #pragma unroll
     for (int g = 0; g < G; ++g) {
+      float* const tile = at + g * kTile;
+      int* const klist = reinterpret_cast<int*>(tile + KS * 4);
       unsigned bits = 0;
       int taken = 0;
+      bool take[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const bool take = pc[g][u] < k1;
-        if (take) {
-          at[(g * KS + (pc[g][u] - k0)) * 4 + r_lane] = pv[g][u];
-          bits |= 1u << (pc[g][u] - k0);
-        }
-        taken += __popc(__ballot_sync(kFullMask, take) & (0xffu << (r_lane * 8)));
+        take[u] = pc[g][u] < k1;
+        if (take[u]) bits |= 1u << (pc[g][u] - k0);
+        taken += __popc(__ballot_sync(kFullMask, take[u]) & (0xffu << (r_lane * 8)));
       }
       pos[g] += taken;
-      // Rare: a row has more than 8*U entries in this slab -- keep consuming synchronously.
-      bool full_batch = taken == 8 * U;
-      while (__any_sync(kFullMask, full_batch)) {
-        const int idx = pos[g] + t_lane;
-        const bool in = full_batch && idx < endp[g];
-        const int c = in ? __ldg(cols + idx) : 0x7fffffff;
-        const bool take = c < k1;
-        if (take) {
-          at[(g * KS + (c - k0)) * 4 + r_lane] = __ldg(vals + idx);
-          bits |= 1u << (c - k0);
+      if (__any_sync(kFullMask, taken == 8 * U)) {
+        // Rare (U is sized from the density): a row has more than 8*U entries in this slab.
+        // Fall back to a dense [KS x 4] tile for this slab and consume synchronously.
+        unsigned mask = __reduce_or_sync(kFullMask, bits);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (take[u]) tile[(pc[g][u] - k0) * 4 + r_lane] = pv[g][u];
+        bool more = taken == 8 * U;
+        while (__any_sync(kFullMask, more)) {
+          const int idx = pos[g] + t_lane;
+          const bool in = more && idx < endp[g];
+          const int c = in ? __ldg(cols + idx) : 0x7fffffff;
+          const bool tk = c < k1;
+          unsigned b2 = 0;
+          if (tk) {
+            tile[(c - k0) * 4 + r_lane] = __ldg(vals + idx);
+            b2 = 1u << (c - k0);
+          }
+          mask |= __reduce_or_sync(kFullMask, b2);
+          const int got = __popc(__ballot_sync(kFullMask, tk) & (0xffu << (r_lane * 8)));
+          pos[g] += got;
+          more = got == 8;
         }
-        const int got = __popc(__ballot_sync(kFullMask, take) & (0xffu << (r_lane * 8)));
-        pos[g] += got;
-        full_batch = got == 8;
+        __syncwarp();
+        // compact in place: entry rank(j) <- slot j (rank(j) <= j, ascending j keeps it safe
+        // because the whole tile is read into registers before it is rewritten).
+        const float4 mine = reinterpret_cast<const float4*>(tile)[lane];
+        __syncwarp();
+        if ((mask >> lane) & 1u) {
+          const int rk = __popc(mask & ((1u << lane) - 1u));
+          reinterpret_cast<float4*>(tile)[rk] = mine;
+          klist[rk] = lane * (NT * 4);
+        }
+        cnts[g] = __popc(mask);
+      } else {
+        const unsigned mask = __reduce_or_sync(kFullMask, bits);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (take[u]) {
+            const int rk = __popc(mask & ((1u << (pc[g][u] - k0)) - 1u));
+            tile[rk * 4 + r_lane] = pv[g][u];
+          }
+        if ((mask >> lane) & 1u) klist[__popc(mask & ((1u << lane) - 1u))] = lane * (NT * 4);
+        cnts[g] = __popc(mask);
       }
-      masks[g] = __reduce_or_sync(kFullMask, bits);
     }
     __syncwarp();
     prefetch();  // for slab s+1; the loads fly under the FMA loop below
 
     mbar_wait(full + st, use & 1);
-    const float* const bs = b_ring + st * Cfg::kSlabFloats + lane * 4;
+    const char* const bs = reinterpret_cast<const char*>(b_ring + st * Cfg::kSlabFloats + lane * 4);
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-      unsigned mk = masks[g];
-      const float* const ag = at + g * KS * 4;
-      while (mk) {
-        const int kk = __ffs(mk) - 1;
-        mk &= mk - 1;
-        const float4 av = *reinterpret_cast<const float4*>(ag + kk * 4);
+      const float* const tile = at + g * kTile;
+      const int* const klist = reinterpret_cast<const int*>(tile + KS * 4);
+      const int cnt = cnts[g];
+      auto column = [&](const float4 av, const int koff) {
         ulonglong2 bv[NV4];
 #pragma unroll
         for (int j = 0; j < NV4; ++j)
-          bv[j] = *reinterpret_cast<const ulonglong2*>(bs + kk * NT + j * 128);
+          bv[j] = *reinterpret_cast<const ulonglong2*>(bs + koff + j * 512);
         const unsigned long long a2[4] = {pack2(av.x, av.x), pack2(av.y, av.y), pack2(av.z, av.z),
                                           pack2(av.w, av.w)};
 #pragma unroll
@@ -232,7 +263,16 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
             fma2(acc[g][r][2 * j], a2[r], bv[j].x);
             fma2(acc[g][r][2 * j + 1], a2[r], bv[j].y);
           }
+      };
+      int i = 0;
+      for (; i + 2 <= cnt; i += 2) {
+        const int2 ko = *reinterpret_cast<const int2*>(klist + i);
+        const float4 av0 = reinterpret_cast<const float4*>(tile)[i];
+        const float4 av1 = reinterpret_cast<const float4*>(tile)[i + 1];
+        column(av0, ko.x);
+        column(av1, ko.y);
       }
+      if (i < cnt) column(reinterpret_cast<const float4*>(tile)[i], klist[i]);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + st);
@@ -302,9 +342,27 @@ inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stre
       a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
   TSP_CHECK_LAUNCH("tsp_spmm_f32 (sorted check)");
 
+  // Candidates prefetched per row per slab = 8*U; sized so that a row's count in a 32-column
+  // slab (mean a = 32*density) almost never exceeds it: U = ceil((a + 3*sqrt(a) + 1) / 8).
+  const double avg = 32.0 * (double)a.nnz / ((double)a.m * (double)a.k);
+  int U = (int)ceil((avg + 3.0 * sqrt(avg) + 1.0) / 8.0);
+  U = U < 1 ? 1 : (U > 4 ? 4 : U);
   int rc;
-  if (a.n > 128) rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 8, 2>>(a, replicas, guard, stream);
-  else rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 2>>(a, replicas, guard, stream);
+  if (a.n > 128) {
+    switch (U) {
+      case 1: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 1>>(a, replicas, guard, stream); break;
+      case 2: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 2>>(a, replicas, guard, stream); break;
+      case 3: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 3>>(a, replicas, guard, stream); break;
+      default: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 4>>(a, replicas, guard, stream); break;
+    }
+  } else {
+    switch (U) {
+      case 1: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 1>>(a, replicas, guard, stream); break;
+      case 2: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 2>>(a, replicas, guard, stream); break;
+      case 3: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 3>>(a, replicas, guard, stream); break;
+      default: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 4>>(a, replicas, guard, stream); break;
+    }
+  }
   if (rc != 0) return rc;
   TSP_CHECK_LAUNCH("tsp_spmm_f32 (staged)");
 
