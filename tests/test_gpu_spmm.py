@@ -151,10 +151,12 @@ def test_spmm_bias_relu(ops, dev):
     assert np.all(got >= 0)
 
 
-@pytest.mark.parametrize("variant", [1, 2])
-def test_spmm_variants_agree(ops, dev, variant):
-    """Forced kernel variants (1 = gather, 2 = staged when applicable) all meet the tolerance."""
-    a, b = spmm_case(512, 768, 512, density=0.15, seed=13, values="pm1")
+@pytest.mark.parametrize("density", [0.03, 0.15, 0.45, 0.9])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
+def test_spmm_variants_agree(ops, dev, variant, density):
+    """Forced kernel variants (1 = gather, 2 = staged, 3/4 = staged with 4/8-row groups) all meet
+    the tolerance, including densities where a row overflows the prefetched candidates."""
+    a, b = spmm_case(520, 777, 512, density=density, seed=13, values="pm1")
     prev = ops.set_variant("spmm", variant)
     try:
         check_spmm(ops, dev, a, b, f"variant {variant}")

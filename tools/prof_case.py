@@ -16,6 +16,8 @@ op, d = sys.argv[1], float(sys.argv[2])
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 n = int(sys.argv[4]) if len(sys.argv) > 4 else 4096
 dim = 4096
+if os.environ.get("TSP_VARIANT"):
+    ops.set_variant(op if op in ("spmm", "sddmm") else "spmm", int(os.environ["TSP_VARIANT"]))
 dev = torch.device("cuda:0")
 a = random_csr(dim, dim, d, seed=0, values="pm1")
 t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev)

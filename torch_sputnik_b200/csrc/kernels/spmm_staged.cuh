@@ -56,19 +56,22 @@ __device__ __forceinline__ void fma2(unsigned long long& d, unsigned long long a
   asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
 
-template <int NV4_, int G_, int STAGES_, int WARPS_, int U_>
+template <int NV4_, int R_, int G_, int STAGES_, int WARPS_, int U_>
 struct StagedCfg {
+  static constexpr int R = R_;            // rows merged per group (4 or 8)
+  static constexpr int LPR = 32 / R_;     // lanes (= candidate slots per batch) per row
   static constexpr int NV4 = NV4_;        // float4 chunks of B per lane
   static constexpr int NT = 128 * NV4_;   // output columns per CTA
-  static constexpr int G = G_;            // 4-row groups per warp
+  static constexpr int G = G_;            // R-row groups per warp
   static constexpr int KS = 32;           // slab depth == width of the occupancy mask
   static constexpr int STAGES = STAGES_;
   static constexpr int WARPS = WARPS_;    // compute warps (+1 producer warp)
-  static constexpr int U = U_;            // prefetched candidates per row per slab = 8*U
-  static constexpr int RB = WARPS_ * G_ * 4;  // rows per CTA
+  static constexpr int U = U_;            // prefetched candidates per row per slab = LPR*U
+  static constexpr int RB = WARPS_ * G_ * R_;  // rows per CTA
   static constexpr int THREADS = (WARPS_ + 1) * 32;
   static constexpr size_t kSlabFloats = (size_t)KS * NT;
-  static constexpr int kTileFloats = KS * 4 + KS;
+  // R values per occupied column + the column's byte offset
+  static constexpr int kTileFloats = KS * R_ + KS;
   static constexpr size_t kSmemBytes =
       sizeof(float) * (STAGES_ * kSlabFloats + (size_t)WARPS_ * G_ * kTileFloats) + 2 * STAGES_ * 8 + 128;
 };
@@ -82,7 +85,7 @@ template <class Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS, (Cfg::kSmemBytes <= 110 * 1024) ? 2 : 1)
 spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   constexpr int NV4 = Cfg::NV4, NT = Cfg::NT, G = Cfg::G, KS = Cfg::KS, STAGES = Cfg::STAGES,
-                WARPS = Cfg::WARPS, U = Cfg::U;
+                WARPS = Cfg::WARPS, U = Cfg::U, R = Cfg::R, LPR = Cfg::LPR;
   if (g_unsorted_flag[guard.slot] == guard.call_id) return;  // gather kernel takes over
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -125,7 +128,8 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   }
 
   // ---------------- compute warps ----------------
-  const int r_lane = lane >> 3, t_lane = lane & 7;  // lane <-> (row in group, candidate slot)
+  const int r_lane = lane / LPR, t_lane = lane % LPR;  // lane <-> (row in group, candidate slot)
+  const unsigned row_lanes = ((1u << LPR) - 1u) << (r_lane * LPR);
   const float* __restrict__ vals = a.values + (size_t)rep * a.values_stride;
   const int* __restrict__ cols = a.column_indices;
   constexpr int kTile = Cfg::kTileFloats;  // KS x 4 values + KS column offsets per 4-row group
@@ -134,7 +138,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   int pos[G], endp[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    const int item = blockIdx.x * Cfg::RB + (warp * G + g) * 4 + r_lane;
+    const int item = blockIdx.x * Cfg::RB + (warp * G + g) * R + r_lane;
     pos[g] = endp[g] = 0;
     if (item < a.m) {
       const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
@@ -143,11 +147,11 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
     }
   }
 
-  unsigned long long acc[G][4][NV4 * 2];
+  unsigned long long acc[G][R][NV4 * 2];
 #pragma unroll
   for (int g = 0; g < G; ++g)
 #pragma unroll
-    for (int r = 0; r < 4; ++r)
+    for (int r = 0; r < R; ++r)
 #pragma unroll
       for (int j = 0; j < NV4 * 2; ++j) acc[g][r][j] = 0ull;
 
@@ -159,7 +163,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
     for (int g = 0; g < G; ++g)
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const int idx = pos[g] + u * 8 + t_lane;
+        const int idx = pos[g] + u * LPR + t_lane;
         const bool in = idx < endp[g];
         pc[g][u] = in ? __ldg(cols + idx) : 0x7fffffff;
         pv[g][u] = in ? __ldg(vals + idx) : 0.f;
@@ -177,12 +181,14 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
     //    offset into the B slab.
 #pragma unroll
     for (int g = 0; g < G; ++g)
-      reinterpret_cast<float4*>(at + g * kTile)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < R / 4; ++q)
+        reinterpret_cast<float4*>(at + g * kTile)[lane + 32 * q] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
 #pragma unroll
     for (int g = 0; g < G; ++g) {
       float* const tile = at + g * kTile;
-      int* const klist = reinterpret_cast<int*>(tile + KS * 4);
+      int* const klist = reinterpret_cast<int*>(tile + KS * R);
       unsigned bits = 0;
       int taken = 0;
       bool take[U];
@@ -190,17 +196,17 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
       for (int u = 0; u < U; ++u) {
         take[u] = pc[g][u] < k1;
         if (take[u]) bits |= 1u << (pc[g][u] - k0);
-        taken += __popc(__ballot_sync(kFullMask, take[u]) & (0xffu << (r_lane * 8)));
+        taken += __popc(__ballot_sync(kFullMask, take[u]) & row_lanes);
       }
       pos[g] += taken;
-      if (__any_sync(kFullMask, taken == 8 * U)) {
+      if (__any_sync(kFullMask, taken == LPR * U)) {
         // Rare (U is sized from the density): a row has more than 8*U entries in this slab.
         // Fall back to a dense [KS x 4] tile for this slab and consume synchronously.
         unsigned mask = __reduce_or_sync(kFullMask, bits);
 #pragma unroll
         for (int u = 0; u < U; ++u)
-          if (take[u]) tile[(pc[g][u] - k0) * 4 + r_lane] = pv[g][u];
-        bool more = taken == 8 * U;
+          if (take[u]) tile[(pc[g][u] - k0) * R + r_lane] = pv[g][u];
+        bool more = taken == LPR * U;
         while (__any_sync(kFullMask, more)) {
           const int idx = pos[g] + t_lane;
           const bool in = more && idx < endp[g];
@@ -208,22 +214,25 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
           const bool tk = c < k1;
           unsigned b2 = 0;
           if (tk) {
-            tile[(c - k0) * 4 + r_lane] = __ldg(vals + idx);
+            tile[(c - k0) * R + r_lane] = __ldg(vals + idx);
             b2 = 1u << (c - k0);
           }
           mask |= __reduce_or_sync(kFullMask, b2);
-          const int got = __popc(__ballot_sync(kFullMask, tk) & (0xffu << (r_lane * 8)));
+          const int got = __popc(__ballot_sync(kFullMask, tk) & row_lanes);
           pos[g] += got;
-          more = got == 8;
+          more = got == LPR;
         }
         __syncwarp();
         // compact in place: entry rank(j) <- slot j (rank(j) <= j, ascending j keeps it safe
         // because the whole tile is read into registers before it is rewritten).
-        const float4 mine = reinterpret_cast<const float4*>(tile)[lane];
+        float4 mine[R / 4];
+#pragma unroll
+        for (int q = 0; q < R / 4; ++q) mine[q] = reinterpret_cast<const float4*>(tile)[lane * (R / 4) + q];
         __syncwarp();
         if ((mask >> lane) & 1u) {
           const int rk = __popc(mask & ((1u << lane) - 1u));
-          reinterpret_cast<float4*>(tile)[rk] = mine;
+#pragma unroll
+          for (int q = 0; q < R / 4; ++q) reinterpret_cast<float4*>(tile)[rk * (R / 4) + q] = mine[q];
           klist[rk] = lane * (NT * 4);
         }
         cnts[g] = __popc(mask);
@@ -233,7 +242,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
         for (int u = 0; u < U; ++u)
           if (take[u]) {
             const int rk = __popc(mask & ((1u << (pc[g][u] - k0)) - 1u));
-            tile[rk * 4 + r_lane] = pv[g][u];
+            tile[rk * R + r_lane] = pv[g][u];
           }
         if ((mask >> lane) & 1u) klist[__popc(mask & ((1u << lane) - 1u))] = lane * (NT * 4);
         cnts[g] = __popc(mask);
@@ -247,32 +256,36 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
 #pragma unroll
     for (int g = 0; g < G; ++g) {
       const float* const tile = at + g * kTile;
-      const int* const klist = reinterpret_cast<const int*>(tile + KS * 4);
+      const int* const klist = reinterpret_cast<const int*>(tile + KS * R);
       const int cnt = cnts[g];
-      auto column = [&](const float4 av, const int koff) {
+      auto column = [&](const int i, const int koff) {
+        float4 av[R / 4];
+#pragma unroll
+        for (int q = 0; q < R / 4; ++q) av[q] = reinterpret_cast<const float4*>(tile)[i * (R / 4) + q];
         ulonglong2 bv[NV4];
 #pragma unroll
         for (int j = 0; j < NV4; ++j)
           bv[j] = *reinterpret_cast<const ulonglong2*>(bs + koff + j * 512);
-        const unsigned long long a2[4] = {pack2(av.x, av.x), pack2(av.y, av.y), pack2(av.z, av.z),
-                                          pack2(av.w, av.w)};
 #pragma unroll
-        for (int r = 0; r < 4; ++r)
+        for (int q = 0; q < R / 4; ++q) {
+          const unsigned long long a2[4] = {pack2(av[q].x, av[q].x), pack2(av[q].y, av[q].y),
+                                            pack2(av[q].z, av[q].z), pack2(av[q].w, av[q].w)};
 #pragma unroll
-          for (int j = 0; j < NV4; ++j) {
-            fma2(acc[g][r][2 * j], a2[r], bv[j].x);
-            fma2(acc[g][r][2 * j + 1], a2[r], bv[j].y);
-          }
+          for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int j = 0; j < NV4; ++j) {
+              fma2(acc[g][q * 4 + r][2 * j], a2[r], bv[j].x);
+              fma2(acc[g][q * 4 + r][2 * j + 1], a2[r], bv[j].y);
+            }
+        }
       };
       int i = 0;
       for (; i + 2 <= cnt; i += 2) {
         const int2 ko = *reinterpret_cast<const int2*>(klist + i);
-        const float4 av0 = reinterpret_cast<const float4*>(tile)[i];
-        const float4 av1 = reinterpret_cast<const float4*>(tile)[i + 1];
-        column(av0, ko.x);
-        column(av1, ko.y);
+        column(i, ko.x);
+        column(i + 1, ko.y);
       }
-      if (i < cnt) column(reinterpret_cast<const float4*>(tile)[i], klist[i]);
+      if (i < cnt) column(i, klist[i]);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + st);
@@ -282,8 +295,8 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
 #pragma unroll
   for (int g = 0; g < G; ++g)
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const int item = blockIdx.x * Cfg::RB + (warp * G + g) * 4 + r;
+    for (int r = 0; r < R; ++r) {
+      const int item = blockIdx.x * Cfg::RB + (warp * G + g) * R + r;
       if (item >= a.m) continue;
       const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
       const float bias = a.bias ? __ldg(a.bias + row) : 0.f;
@@ -333,7 +346,9 @@ inline int launch_spmm_staged_cfg(const SpmmArgs& a, int replicas, const StagedG
 static std::atomic<unsigned> g_call_counter{0};
 
 // Returns TSP_OK / an error code, or -1 if the staged path declines (caller uses gather).
-inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stream) {
+// rows_per_group: 0 = pick from the density, 4 or 8 = forced (benchmark knob).
+inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stream,
+                              int rows_per_group = 0) {
   unsigned id = g_call_counter.fetch_add(1) + 1;
   if (id == 0) id = g_call_counter.fetch_add(1) + 1;
   StagedGuard guard{(int)(id % kFlagSlots), id};
@@ -342,25 +357,34 @@ inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stre
       a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
   TSP_CHECK_LAUNCH("tsp_spmm_f32 (sorted check)");
 
-  // Candidates prefetched per row per slab = 8*U; sized so that a row's count in a 32-column
-  // slab (mean a = 32*density) almost never exceeds it: U = ceil((a + 3*sqrt(a) + 1) / 8).
-  const double avg = 32.0 * (double)a.nnz / ((double)a.m * (double)a.k);
-  int U = (int)ceil((avg + 3.0 * sqrt(avg) + 1.0) / 8.0);
-  U = U < 1 ? 1 : (U > 4 ? 4 : U);
+  // Candidates prefetched per row per slab = LPR*U; sized so that a row's count in a 32-column
+  // slab (mean avg = 32*density) almost never exceeds it.
+  const double density = (double)a.nnz / ((double)a.m * (double)a.k);
+  const double avg = 32.0 * density;
+  const double want = avg + 3.0 * sqrt(avg) + 1.0;
+  // Eight merged rows pay once nearly every column of a slab is occupied anyway.
+  const int R = rows_per_group ? rows_per_group : (density >= 0.45 && a.n > 128 ? 8 : 4);
   int rc;
-  if (a.n > 128) {
-    switch (U) {
-      case 1: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 1>>(a, replicas, guard, stream); break;
-      case 2: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 2>>(a, replicas, guard, stream); break;
-      case 3: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 3>>(a, replicas, guard, stream); break;
-      default: rc = launch_spmm_staged_cfg<StagedCfg<2, 2, 3, 7, 4>>(a, replicas, guard, stream); break;
-    }
+  if (R == 8) {
+    if (want <= 24.0) rc = launch_spmm_staged_cfg<StagedCfg<2, 8, 1, 3, 7, 6>>(a, replicas, guard, stream);
+    else rc = launch_spmm_staged_cfg<StagedCfg<2, 8, 1, 3, 7, 8>>(a, replicas, guard, stream);
   } else {
-    switch (U) {
-      case 1: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 1>>(a, replicas, guard, stream); break;
-      case 2: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 2>>(a, replicas, guard, stream); break;
-      case 3: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 3>>(a, replicas, guard, stream); break;
-      default: rc = launch_spmm_staged_cfg<StagedCfg<1, 2, 4, 8, 4>>(a, replicas, guard, stream); break;
+    int U = (int)ceil(want / 8.0);
+    U = U < 1 ? 1 : (U > 4 ? 4 : U);
+    if (a.n > 128) {
+      switch (U) {
+        case 1: rc = launch_spmm_staged_cfg<StagedCfg<2, 4, 2, 3, 7, 1>>(a, replicas, guard, stream); break;
+        case 2: rc = launch_spmm_staged_cfg<StagedCfg<2, 4, 2, 3, 7, 2>>(a, replicas, guard, stream); break;
+        case 3: rc = launch_spmm_staged_cfg<StagedCfg<2, 4, 2, 3, 7, 3>>(a, replicas, guard, stream); break;
+        default: rc = launch_spmm_staged_cfg<StagedCfg<2, 4, 2, 3, 7, 4>>(a, replicas, guard, stream); break;
+      }
+    } else {
+      switch (U) {
+        case 1: rc = launch_spmm_staged_cfg<StagedCfg<1, 4, 2, 4, 8, 1>>(a, replicas, guard, stream); break;
+        case 2: rc = launch_spmm_staged_cfg<StagedCfg<1, 4, 2, 4, 8, 2>>(a, replicas, guard, stream); break;
+        case 3: rc = launch_spmm_staged_cfg<StagedCfg<1, 4, 2, 4, 8, 3>>(a, replicas, guard, stream); break;
+        default: rc = launch_spmm_staged_cfg<StagedCfg<1, 4, 2, 4, 8, 4>>(a, replicas, guard, stream); break;
+      }
     }
   }
   if (rc != 0) return rc;

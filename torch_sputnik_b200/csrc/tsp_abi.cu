@@ -98,9 +98,16 @@ int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
   const bool vec2_ok = (n % 2 == 0) && ((reinterpret_cast<uintptr_t>(dense) & 7u) == 0) &&
                        ((reinterpret_cast<uintptr_t>(out) & 7u) == 0);
 
+  // variant: 0 = heuristic, 1 = gather, 2 = staged (rows per group from density), 3 = staged with
+  // 4-row groups, 4 = staged with 8-row groups.
   if (variant != 1 && spmm_staged_applicable(a, replicas)) {
-    const int rc = launch_spmm_staged(a, replicas, stream);
-    if (rc >= 0) return rc;  // < 0: staged path declined, use the gather kernel
+    const double density = (double)nnz / ((double)m * (double)k);
+    // Below ~22 % density (measured crossover on B200, profiles/) rows of a group share almost no columns, merging cannot raise the FMA
+    // per shared-memory wavefront ratio, and the L1/L2 gather kernel has less fixed cost per slab.
+    if (variant != 0 || density >= 0.22) {
+      const int rc = launch_spmm_staged(a, replicas, stream, variant == 3 ? 4 : (variant == 4 ? 8 : 0));
+      if (rc >= 0) return rc;  // < 0: staged path declined, use the gather kernel
+    }
   }
 
   if (vec4_ok && n > 128) {
