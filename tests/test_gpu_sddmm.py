@@ -92,6 +92,37 @@ def test_sddmm_variants_agree(ops, dev, variant):
         ops.set_variant("sddmm", prev)
 
 
+@pytest.mark.parametrize("m,n,k,density,reps", [(130, 70, 132, 0.3, 1), (64, 64, 128, 1.0, 1), (300, 513, 260, 0.05, 3),
+                                                 (1000, 200, 512, 0.6, 2), (129, 4097, 128, 0.25, 1)])
+def test_sddmm_tiled_ragged_shapes(ops, dev, m, n, k, density, reps):
+    """Forced tiled variant at shapes that do not divide the 128 x 64 x 32 tile, with replicas."""
+    a = random_csr(m, n, density, seed=m + n + k, values="pm1")
+    lead = (reps,) if reps > 1 else ()
+    lhs, rhs = dense_operand(lead + (m, k), 21, "pm1"), dense_operand(lead + (n, k), 22, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    prev = ops.set_variant("sddmm", 2)
+    try:
+        got = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev)).cpu().numpy()
+    finally:
+        ops.set_variant("sddmm", prev)
+    ref = oracle.sddmm(m, n, a.row_offsets, a.column_indices, lhs, rhs)
+    for r in range(reps):
+        g, f = (got[r], ref[r]) if reps > 1 else (got, ref)
+        scale = oracle.sddmm_abs(m, n, a.row_offsets, a.column_indices, lhs[r] if reps > 1 else lhs,
+                                 rhs[r] if reps > 1 else rhs)
+        assert_close_fwd(g, f, scale, what=f"tiled {m}x{n}x{k} replica {r}")
+
+
+def test_sddmm_unsorted_columns_fall_back(ops, dev):
+    """Shuffled column order inside rows: the tiled kernel must step aside for the gather kernel."""
+    a = random_csr(256, 320, 0.4, seed=23, values="pm1")
+    rng = np.random.default_rng(3)
+    for i in range(a.m):
+        s, e = a.row_offsets[i], a.row_offsets[i + 1]
+        a.column_indices[s:e] = a.column_indices[s:e][rng.permutation(e - s)]
+    check_sddmm(ops, dev, a, dense_operand((256, 256), 24, "pm1"), dense_operand((320, 256), 25, "pm1"), "unsorted")
+
+
 def test_sddmm_attention_shape(ops, dev):
     """BASELINE.json configs[3] shape per replica: s=4096, d=64, 90 % sparse; 2 replicas here."""
     a = random_csr(4096, 4096, 0.1, seed=14, values="u01")

@@ -13,7 +13,7 @@
 // Arithmetic matches sputnik::CudaSddmmKernel (cuda_sddmm.cu.cc:34-165): fp32 FMA along k per
 // lane, then fp32 tree sum across lanes.
 #pragma once
-#include "common.cuh"
+#include "spmm_gather.cuh"  // g_unsorted_flag
 
 namespace tsp {
 
@@ -24,6 +24,10 @@ struct SddmmArgs {
   const float* lhs;  // [replicas, m, k]
   const float* rhs;  // [replicas, n, k]
   float* out;        // [replicas, nnz]
+  // guard_id != 0: this launch is the unsorted-columns fallback of a tiled launch and runs only
+  // if g_unsorted_flag[guard_slot] == guard_id.
+  int guard_slot = 0;
+  unsigned guard_id = 0;
 };
 
 // Row containing flat nonzero j: largest i with row_offsets[i] <= j (skips empty rows).
@@ -58,6 +62,7 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   constexpr int NPG = LPN;     // nonzeros per group per chunk (G * NPG == 32)
   constexpr int KSTEP = LPN * VEC;
 
+  if (a.guard_id != 0 && g_unsorted_flag[a.guard_slot] != a.guard_id) return;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int chunk = blockIdx.x * WARPS + warp;

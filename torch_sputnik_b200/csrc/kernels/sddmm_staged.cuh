@@ -1,7 +1,3 @@
-// sddmm_staged.cuh -- placeholder until the staged SDDMM kernel lands.
+// sddmm_staged.cuh -- entry points of the non-gather SDDMM variants (see sddmm_tiled.cuh).
 #pragma once
-#include "sddmm_gather.cuh"
-namespace tsp {
-inline bool sddmm_staged_applicable(const SddmmArgs&, int) { return false; }
-inline int launch_sddmm_staged(const SddmmArgs&, int, cudaStream_t) { return -1; }
-}  // namespace tsp
+#include "sddmm_tiled.cuh"

@@ -149,10 +149,15 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
   a.rhs = rhs;
   a.out = out;
 
+  // variant: 0 = heuristic, 1 = gather, 2 = tiled (dense register tiles, sampled).
   const int variant = g_sddmm_variant.load();
-  if (variant != 1 && sddmm_staged_applicable(a, replicas)) {
-    const int rc = launch_sddmm_staged(a, replicas, stream);
-    if (rc >= 0) return rc;
+  const double density = (double)nnz / ((double)m * (double)n);
+  if (variant != 1 && sddmm_tiled_applicable(a, replicas) && (variant == 2 || density >= 0.2)) {
+    StagedGuard guard;
+    const int rc = launch_sddmm_tiled(a, replicas, stream, &guard);
+    if (rc != 0) return rc;
+    a.guard_slot = guard.slot;   // the gather launch below becomes the unsorted-columns fallback
+    a.guard_id = guard.call_id;
   }
 
   const bool vec4_ok = (k % 4 == 0) && aligned16(lhs) && aligned16(rhs);
