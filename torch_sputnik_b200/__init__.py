@@ -26,7 +26,7 @@ def _load_extension():
     if not (os.path.exists(path) and os.path.exists(lib)):
         raise ImportError(
             "torch_sputnik_b200: native extension not built (expected %s and %s). "
-            "Run `python -m torch_sputnik_b200.build` (needs nvcc, sm_100a). "
+            "Run `python torch_sputnik_b200/build.py` (needs nvcc, sm_100a). "
             "There is no CPU fallback." % (path, lib))
     spec = importlib.util.spec_from_file_location("torch_sputnik", path)
     mod = importlib.util.module_from_spec(spec)

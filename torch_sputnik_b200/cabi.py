@@ -22,7 +22,7 @@ def load() -> ctypes.CDLL:
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
-            raise ImportError(f"{LIB_PATH} not built; run `python -m torch_sputnik_b200.build`")
+            raise ImportError(f"{LIB_PATH} not built; run `python torch_sputnik_b200/build.py`")
         lib = ctypes.CDLL(LIB_PATH)
         i, vp, f, sz = ctypes.c_int, ctypes.c_void_p, ctypes.c_float, ctypes.c_size_t
         lib.tsp_version.restype = i
