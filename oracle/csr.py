@@ -106,3 +106,18 @@ def dense_operand(shape, seed: int, dist: str = "u01") -> np.ndarray:
     if dist == "pm1":
         x = (x * 2.0 - 1.0).astype(np.float32)
     return x
+
+
+def from_dense_mask(mask: np.ndarray, seed: int = 0, values: str = "pm1") -> Csr:
+    """CSR of an arbitrary boolean mask (skewed-pattern test cases), columns ascending per row."""
+    m, k = mask.shape
+    rows, cols = np.nonzero(mask)
+    row_offsets = np.zeros(m + 1, dtype=np.int64)
+    np.add.at(row_offsets, rows + 1, 1)
+    row_offsets = np.cumsum(row_offsets).astype(np.int32)
+    rng = np.random.default_rng(seed)
+    vals = rng.random(rows.shape[0], dtype=np.float32)
+    if values == "pm1":
+        vals = (vals * 2.0 - 1.0).astype(np.float32)
+    vals[vals == 0.0] = 0.5
+    return Csr(m, k, vals, sorted_row_swizzle(row_offsets), row_offsets, cols.astype(np.int32))

@@ -81,7 +81,7 @@ def test_sddmm_replicated_3d_and_quirks(ops, dev):
     assert tuple(one.shape) == (a.nnz,)
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 def test_sddmm_variants_agree(ops, dev, variant):
     a = random_csr(512, 640, 0.15, seed=11, values="pm1")
     prev = ops.set_variant("sddmm", variant)
@@ -111,6 +111,51 @@ def test_sddmm_tiled_ragged_shapes(ops, dev, m, n, k, density, reps):
         scale = oracle.sddmm_abs(m, n, a.row_offsets, a.column_indices, lhs[r] if reps > 1 else lhs,
                                  rhs[r] if reps > 1 else rhs)
         assert_close_fwd(g, f, scale, what=f"tiled {m}x{n}x{k} replica {r}")
+
+
+@pytest.mark.parametrize("m,n,k,density,reps,bn", [
+    (130, 70, 260, 0.3, 1, 0), (128, 64, 256, 1.0, 1, 0), (300, 513, 260, 0.05, 3, 0), (1000, 200, 512, 0.1, 2, 0),
+    (129, 4097, 256, 0.02, 1, 0), (512, 512, 1028, 0.5, 1, 128), (256, 300, 256, 0.9, 1, 256), (640, 384, 300, 0.15, 2, 48)])
+def test_sddmm_sampled_ragged_shapes(ops, dev, m, n, k, density, reps, bn):
+    """Forced sampled variant: ragged shapes, k tails, replicas, and tiles that overflow the 32*P
+    register slots (dense masks / wide forced tiles -> several rounds per tile)."""
+    a = random_csr(m, n, density, seed=m + n + k, values="pm1")
+    lead = (reps,) if reps > 1 else ()
+    lhs, rhs = dense_operand(lead + (m, k), 31, "pm1"), dense_operand(lead + (n, k), 32, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    prev = ops.set_variant("sddmm", 3)
+    prev_bn = ops.set_variant("sddmm_bn", bn)
+    try:
+        out = torch.full(lead + (a.nnz,), float("nan"), device=dev)  # noqa: F841 (poison the allocator's next block)
+        del out
+        got = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev)).cpu().numpy()
+    finally:
+        ops.set_variant("sddmm", prev)
+        ops.set_variant("sddmm_bn", prev_bn)
+    assert not np.isnan(got).any()
+    ref = oracle.sddmm(m, n, a.row_offsets, a.column_indices, lhs, rhs)
+    for r in range(reps):
+        g, f = (got[r], ref[r]) if reps > 1 else (got, ref)
+        scale = oracle.sddmm_abs(m, n, a.row_offsets, a.column_indices, lhs[r] if reps > 1 else lhs,
+                                 rhs[r] if reps > 1 else rhs)
+        assert_close_fwd(g, f, scale, what=f"sampled {m}x{n}x{k} replica {r}")
+
+
+def test_sddmm_sampled_empty_rows_and_skew(ops, dev):
+    """Rows with no nonzeros, one fully dense row block and an empty column band."""
+    m, n, k = 384, 512, 256
+    rng = np.random.default_rng(5)
+    dense = (rng.random((m, n)) < 0.08)
+    dense[10:40] = False
+    dense[128:256, :200] = True
+    dense[:, 300:360] = False
+    from oracle.csr import from_dense_mask
+    a = from_dense_mask(dense, seed=6, values="pm1")
+    prev = ops.set_variant("sddmm", 3)
+    try:
+        check_sddmm(ops, dev, a, dense_operand((m, k), 33, "pm1"), dense_operand((n, k), 34, "pm1"), "sampled skew")
+    finally:
+        ops.set_variant("sddmm", prev)
 
 
 def test_sddmm_unsorted_columns_fall_back(ops, dev):

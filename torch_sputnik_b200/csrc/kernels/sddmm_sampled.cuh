@@ -1,0 +1,307 @@
+// sddmm_sampled.cuh -- SDDMM, variant 3 ("sampled"): operands staged in shared memory by TMA, only
+// the sampled products computed.  The path for 2 % .. 20 % dense masks with a long inner dimension.
+//
+// out[j] = <lhs[row_of(j), :], rhs[col(j), :]>.  The gather SDDMM (variant 1, and the reference,
+// sddmm/cuda_sddmm.cu.cc:34-165) pulls a K-long rhs row through L1/L2 for every nonzero; the tiled
+// variant computes all BM x BN products and throws (1 - d) of them away.  Between the two:
+//
+//  * a CTA owns a [128 rows x BN cols] tile of the mask (BN sized from the density so the tile holds
+//    ~1400 nonzeros) for the whole K loop; per 32-deep k-slab two TMA tensor-map loads bring the
+//    128 lhs rows and BN rhs rows (128 B each) into a shared-memory ring (mbarrier complete_tx),
+//    so every operand byte crosses L2 -> SM once per tile instead of once per nonzero;
+//  * the tile's nonzeros are flattened (row-major) and dealt evenly to the 32 eight-lane groups
+//    of the CTA, P slots each, as packed (rhs offset | lhs offset | new-row) words held in
+//    REGISTERS for the whole K loop, next to P fp32 accumulators per lane;
+//  * per slab and nonzero a group issues ONE LDS.128 (each lane its 16-byte k-slice of the rhs
+//    row; the 8 lanes cover the 128-byte row, so a quarter-warp reads one full row: 4 wavefronts
+//    per warp instruction, conflict-free, tools/ubench/ubench_lds.cu pattern 7) and 4 FFMA;
+//    the lhs slice is reloaded only when the row changes (predicated LDS.128);
+//  * after the K loop a transposing butterfly over the 8 lanes (7 shuffles per 8 nonzeros) leaves
+//    one finished dot product per lane, written to out[] through the slot's flat nonzero index.
+//
+// Bound: 4 bytes of shared-memory bandwidth per FMA -> 32 FMA/clk/SM = 25 % of the fp32 pipe
+// (18.6 TFLOP/s); there is no reuse to exploit below ~20 % density.
+// Tiles holding more than 32*P nonzeros (skewed patterns) take extra rounds over the K loop.
+//
+// Precondition: ascending columns per row (device-checked; gather fallback otherwise), k % 4 == 0,
+// 16-byte aligned operands.
+#pragma once
+#include "sddmm_tiled.cuh"
+
+namespace tsp {
+
+template <int P_, int STAGES_>
+struct SddmmSampledCfg {
+  static constexpr int BM = 128, BK = 32, THREADS = 256, GROUPS = 32;
+  static constexpr int P = P_, STAGES = STAGES_;
+  static constexpr int CAP = GROUPS * P_;
+  static size_t smem_bytes(int bn) {
+    return (size_t)STAGES_ * (BM + bn) * BK * 4 + (size_t)CAP * 8 + BM * 4 + (BM + 1) * 4 + 2 * STAGES_ * 8 + 256;
+  }
+};
+
+// starts[row * (nb + 1) + b] = first flat index in row `row` whose column is >= b * bn
+// (b == nb gives the row's end).  Needs ascending columns.
+__global__ void __launch_bounds__(256)
+csr_block_starts_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m, int nb,
+                        int bn, int* __restrict__ starts) {
+  const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (t >= (long long)m * (nb + 1)) return;
+  const int row = (int)(t / (nb + 1)), b = (int)(t % (nb + 1));
+  int lo = __ldg(row_offsets + row), hi = __ldg(row_offsets + row + 1);
+  if (b == nb) {
+    starts[t] = hi;
+    return;
+  }
+  const int target = b * bn;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(cols + mid) < target) lo = mid + 1; else hi = mid;
+  }
+  starts[t] = lo;
+}
+
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::THREADS, 2)
+sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
+                     const int* __restrict__ starts, const __grid_constant__ CUtensorMap tm_lhs,
+                     const __grid_constant__ CUtensorMap tm_rhs) {
+  constexpr int BM = Cfg::BM, BK = Cfg::BK, P = Cfg::P, STAGES = Cfg::STAGES, CAP = Cfg::CAP;
+  if (g_unsorted_flag[guard.slot] == guard.call_id) return;
+
+  extern __shared__ unsigned char smem_dyn[];
+  unsigned char* const smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
+  const int stage_bytes = (BM + bn) * BK * 4;
+  unsigned char* const ring = smem_raw;
+  unsigned* const ent = reinterpret_cast<unsigned*>(ring + (size_t)STAGES * stage_bytes);
+  int* const oidx = reinterpret_cast<int*>(ent + CAP);
+  int* const row_start = oidx + CAP;       // [BM]   flat index of the row's first nonzero in the tile
+  int* const row_off = row_start + BM;     // [BM+1] exclusive prefix of the per-row counts
+  unsigned long long* const full = reinterpret_cast<unsigned long long*>(
+      (reinterpret_cast<uintptr_t>(row_off + BM + 1) + 7) & ~uintptr_t(7));
+  unsigned long long* const empty = full + STAGES;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int grp = tid >> 3, sub = tid & 7;
+  const int rb = blockIdx.x / nb, cb = blockIdx.x % nb;
+  const int rep = blockIdx.y;
+  const int ksteps = (a.k + BK - 1) / BK;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, Cfg::THREADS / 32);
+    }
+    mbar_fence_init();
+  }
+
+  // ---- per-row ranges of this tile and their exclusive prefix (one warp scan over 128 counts) ----
+  if (tid < BM) {
+    const int row = rb * BM + tid;
+    int s = 0, e = 0;
+    if (row < a.m) {
+      const int* p = starts + (size_t)row * (nb + 1) + cb;
+      s = __ldg(p);
+      e = __ldg(p + 1);
+    }
+    row_start[tid] = s;
+    row_off[tid + 1] = e - s;
+  }
+  if (tid == 0) row_off[0] = 0;
+  __syncthreads();
+  if (warp == 0) {
+    int c[4], sum = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      c[i] = row_off[1 + lane * 4 + i];
+      sum += c[i];
+    }
+    int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int v = __shfl_up_sync(kFullMask, incl, d);
+      if (lane >= d) incl += v;
+    }
+    int run = incl - sum;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      run += c[i];
+      row_off[1 + lane * 4 + i] = run;
+    }
+  }
+  __syncthreads();
+  const int total = row_off[BM];
+  if (total == 0) return;
+
+  const int* __restrict__ cols = a.column_indices;
+  float* __restrict__ out = a.out + (size_t)rep * a.nnz;
+  const int c0 = cb * bn;
+  int q = 0;  // slabs consumed so far by this CTA (ring position carries across rounds)
+
+  for (int lo = 0; lo < total; lo += CAP) {
+    const int cnt_round = min(CAP, total - lo);
+    const int per = (cnt_round + Cfg::GROUPS - 1) / Cfg::GROUPS;  // slots in use per group (<= P)
+
+    // ---- deal the round's nonzeros to (group, slot) ----
+    for (int i = tid; i < CAP; i += Cfg::THREADS) {
+      ent[i] = 0u;
+      oidx[i] = -1;
+    }
+    __syncthreads();
+    for (int r = warp; r < BM; r += Cfg::THREADS / 32) {
+      const int off = row_off[r], cnt = row_off[r + 1] - off, s = row_start[r];
+      for (int i = lane; i < cnt; i += 32) {
+        const int el = off + i - lo;
+        if (el < 0 || el >= cnt_round) continue;
+        const int g = el / per, slot = el - g * per;
+        const unsigned col_local = (unsigned)(__ldg(cols + s + i) - c0);
+        const unsigned fresh = (i == 0 || slot == 0) ? 0x80000000u : 0u;
+        ent[g * P + slot] = (col_local * 128u) | ((unsigned)r << 23) | fresh;   // lhs offset = r*128 -> bits 16..30
+        oidx[g * P + slot] = s + i;
+      }
+    }
+    __syncthreads();
+
+    unsigned my[P];
+#pragma unroll
+    for (int e = 0; e < P; ++e) my[e] = ent[grp * P + e];
+    float acc[P];
+#pragma unroll
+    for (int e = 0; e < P; ++e) acc[e] = 0.f;
+
+    // ---- K loop: TMA ring, thread 0 is the producer ----
+    auto issue = [&](int qq) {   // called by thread 0 only
+      const int st = qq % STAGES, use = qq / STAGES;
+      if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
+      unsigned char* const dst = ring + (size_t)st * stage_bytes;
+      const int ks = qq % ksteps;
+      mbar_arrive_expect_tx(full + st, (unsigned)stage_bytes);
+      tma_load_3d(dst, &tm_lhs, ks * BK, rb * BM, rep, full + st);
+      tma_load_3d(dst + BM * BK * 4, &tm_rhs, ks * BK, c0, rep, full + st);
+    };
+    const int q_end = q + ksteps;
+    if (tid == 0)
+      for (int qq = q; qq < min(q_end, q + STAGES - 1); ++qq) issue(qq);
+
+    for (; q < q_end; ++q) {
+      if (tid == 0 && q + STAGES - 1 < q_end) issue(q + STAGES - 1);
+      const int st = q % STAGES;
+      mbar_wait(full + st, (q / STAGES) & 1);
+      const unsigned char* const sl = ring + (size_t)st * stage_bytes + sub * 16;
+      const unsigned char* const sr = sl + BM * BK * 4;
+      float4 l = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int e = 0; e < P; ++e) {
+        const unsigned u = my[e];
+        if ((int)u < 0) l = *reinterpret_cast<const float4*>(sl + ((u >> 16) & 0x7fffu));
+        const float4 r = *reinterpret_cast<const float4*>(sr + (u & 0xffffu));
+        acc[e] = fmaf(l.x, r.x, acc[e]);
+        acc[e] = fmaf(l.y, r.y, acc[e]);
+        acc[e] = fmaf(l.z, r.z, acc[e]);
+        acc[e] = fmaf(l.w, r.w, acc[e]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + st);
+    }
+
+    // ---- reduce the 8 k-slices of every slot, one finished value per lane ----
+#pragma unroll
+    for (int b = 0; b < P / 8; ++b) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = acc[b * 8 + i];
+      transpose_reduce<8>(v, sub);
+      const int j = oidx[grp * P + b * 8 + sub];
+      if (j >= 0) out[j] = v[0];
+    }
+    __syncthreads();  // ent/oidx are rewritten by the next round
+  }
+}
+
+// [replicas][rows][k] fp32, K-contiguous; box = [1][box_rows][32 floats], no swizzle.
+inline bool encode_rowmajor_map_plain(CUtensorMap* tm, const float* base, int replicas, int rows, int k,
+                                      int box_rows) {
+  TensorMapEncodeFn enc = tensor_map_encoder();
+  if (!enc) return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)replicas};
+  const cuuint64_t strides[2] = {(cuuint64_t)k * 4, (cuuint64_t)rows * k * 4};
+  const cuuint32_t box[3] = {32, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+inline bool sddmm_sampled_applicable(const SddmmArgs& a, int replicas) {
+  if (a.k % 4 != 0 || a.k < 256) return false;
+  if (!aligned16(a.lhs) || !aligned16(a.rhs)) return false;
+  if (a.m < 128 || a.n < 64) return false;
+  return 2.0 * a.nnz * a.k * replicas >= 5.0e7;
+}
+
+template <class Cfg>
+inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream_t stream,
+                                    const StagedGuard& guard, int bn) {
+  const int row_blocks = ceil_div(a.m, Cfg::BM), nb = ceil_div(a.n, bn);
+  const size_t smem = Cfg::smem_bytes(bn);
+  static size_t configured[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && configured[dev] < smem) {
+    cudaError_t e = cudaFuncSetAttribute(sddmm_sampled_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)Cfg::smem_bytes(256));
+    if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled smem attribute)");
+    configured[dev] = Cfg::smem_bytes(256);
+  }
+  void* ws = nullptr;
+  cudaError_t e = cudaMallocAsync(&ws, (size_t)a.m * (nb + 1) * 4 + 256, stream);
+  if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled scratch)");
+  int* starts = static_cast<int*>(ws);
+  csr_block_starts_kernel<<<ceil_div((long long)a.m * (nb + 1), 256), 256, 0, stream>>>(
+      a.row_offsets, a.column_indices, a.m, nb, bn, starts);
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (block starts)");
+  CUtensorMap tm_lhs, tm_rhs;
+  if (!encode_rowmajor_map_plain(&tm_lhs, a.lhs, replicas, a.m, a.k, Cfg::BM) ||
+      !encode_rowmajor_map_plain(&tm_rhs, a.rhs, replicas, a.n, a.k, bn)) {
+    cudaFreeAsync(ws, stream);
+    set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
+    return 2;
+  }
+  dim3 grid(row_blocks * nb, replicas);
+  sddmm_sampled_kernel<Cfg><<<grid, Cfg::THREADS, smem, stream>>>(a, guard, nb, bn, starts, tm_lhs, tm_rhs);
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sampled)");
+  cudaFreeAsync(ws, stream);
+  return 0;
+}
+
+// Tile width from the density: the widest multiple of 16 columns (<= 256, <= n) whose expected
+// nonzero count plus three standard deviations still fits the 32*P register slots of a CTA.
+template <class Cfg>
+inline int sddmm_sampled_tile_width(const SddmmArgs& a) {
+  const double density = (double)a.nnz / ((double)a.m * (double)a.n);
+  const double cap = (double)Cfg::CAP;
+  const double mu = (2.0 * cap + 9.0 - 3.0 * sqrt(4.0 * cap + 9.0)) / 2.0;   // mu + 3 sqrt(mu) = cap
+  int bn = (int)(mu / (Cfg::BM * density)) / 16 * 16;
+  const int n16 = a.n / 16 * 16;
+  bn = bn > 256 ? 256 : bn;
+  bn = bn > n16 ? n16 : bn;
+  return bn < 16 ? 16 : bn;
+}
+
+// Returns 0 / an error code.  The gather kernel is launched behind it as the unsorted fallback.
+inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t stream, StagedGuard* guard_out,
+                                int bn_override = 0) {
+  unsigned id = g_call_counter.fetch_add(1) + 1;
+  if (id == 0) id = g_call_counter.fetch_add(1) + 1;
+  StagedGuard guard{(int)(id % kFlagSlots), id};
+  *guard_out = guard;
+  csr_check_sorted_kernel<<<min(ceil_div(a.m, 8), 4 * sm_count()), 256, 0, stream>>>(
+      a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sorted check)");
+  using Cfg = SddmmSampledCfg<48, 2>;
+  const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a);
+  return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
+}
+
+}  // namespace tsp

@@ -13,6 +13,7 @@
 #include "kernels/spmm_gather.cuh"
 #include "kernels/spmm_staged.cuh"
 #include "kernels/sddmm_staged.cuh"
+#include "kernels/sddmm_sampled.cuh"
 
 namespace tsp {
 
@@ -20,6 +21,7 @@ static thread_local char t_error[512] = "";
 std::atomic<unsigned long long> g_launches{0};
 static std::atomic<int> g_spmm_variant{0};
 static std::atomic<int> g_sddmm_variant{0};
+static std::atomic<int> g_sddmm_bn{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -64,6 +66,7 @@ unsigned long long tsp_launch_count(void) { return g_launches.load(); }
 int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm") == 0) return g_spmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
+  if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   return -1;
 }
 
@@ -149,14 +152,23 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
   a.rhs = rhs;
   a.out = out;
 
-  // variant: 0 = heuristic, 1 = gather, 2 = tiled (dense register tiles, sampled).
+  // variant: 0 = heuristic, 1 = gather, 2 = tiled (dense register tiles, sampled), 3 = sampled
+  // (TMA-staged operands, only the sampled products).
   const int variant = g_sddmm_variant.load();
   const double density = (double)nnz / ((double)m * (double)n);
-  if (variant != 1 && sddmm_tiled_applicable(a, replicas) && (variant == 2 || density >= 0.2)) {
+  const bool want_tiled = variant == 2 || (variant == 0 && density >= 0.2);
+  const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.2);
+  if (want_tiled && sddmm_tiled_applicable(a, replicas)) {
     StagedGuard guard;
     const int rc = launch_sddmm_tiled(a, replicas, stream, &guard);
     if (rc != 0) return rc;
     a.guard_slot = guard.slot;   // the gather launch below becomes the unsorted-columns fallback
+    a.guard_id = guard.call_id;
+  } else if (want_sampled && sddmm_sampled_applicable(a, replicas)) {
+    StagedGuard guard;
+    const int rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load());
+    if (rc != 0) return rc;
+    a.guard_slot = guard.slot;
     a.guard_id = guard.call_id;
   }
 
