@@ -16,20 +16,21 @@ WANT = [
     "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
     "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
-    "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
-    "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct",
-    "smsp__warp_issue_stalled_short_scoreboard_per_warp_active.pct",
-    "smsp__warp_issue_stalled_barrier_per_warp_active.pct", "smsp__warp_issue_stalled_wait_per_warp_active.pct",
-    "smsp__warp_issue_stalled_math_pipe_throttle_per_warp_active.pct",
-    "smsp__warp_issue_stalled_mio_throttle_per_warp_active.pct",
-    "smsp__warp_issue_stalled_lg_throttle_per_warp_active.pct",
-    "smsp__warp_issue_stalled_not_selected_per_warp_active.pct",
-    "smsp__warp_issue_stalled_branch_resolving_per_warp_active.pct",
-    "smsp__warp_issue_stalled_dispatch_stall_per_warp_active.pct",
-    "smsp__warp_issue_stalled_no_instruction_per_warp_active.pct",
-    "smsp__warp_issue_stalled_membar_per_warp_active.pct",
-    "smsp__warp_issue_stalled_sleeping_per_warp_active.pct",
-    "smsp__warp_issue_stalled_selected_per_warp_active.pct",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active", "lts__t_bytes.sum", "l1tex__m_xbar2l1tex_read_bytes.sum",
+    "smsp__average_warps_issue_stalled_tex_throttle_per_issue_active.ratio", "smsp__inst_executed.sum",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio", "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_membar_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_sleeping_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_selected_per_issue_active.ratio",
 ]
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))

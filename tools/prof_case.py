@@ -18,6 +18,9 @@ n = int(sys.argv[4]) if len(sys.argv) > 4 else 4096
 dim = 4096
 if os.environ.get("TSP_VARIANT"):
     ops.set_variant(op if op in ("spmm", "sddmm") else "spmm", int(os.environ["TSP_VARIANT"]))
+for knob in ("sddmm_bn", "sddmm_p"):
+    if os.environ.get("TSP_" + knob.upper()):
+        ops.set_variant(knob, int(os.environ["TSP_" + knob.upper()]))
 dev = torch.device("cuda:0")
 a = random_csr(dim, dim, d, seed=0, values="pm1")
 t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev)

@@ -36,7 +36,7 @@ struct SddmmSampledCfg {
   static constexpr int P = P_, STAGES = STAGES_;
   static constexpr int CAP = GROUPS * P_;
   static size_t smem_bytes(int bn) {
-    return (size_t)STAGES_ * (BM + bn) * BK * 4 + (size_t)CAP * 8 + BM * 4 + (BM + 1) * 4 + 2 * STAGES_ * 8 + 256;
+    return (size_t)STAGES_ * (BM + bn) * BK * 4 + (size_t)CAP * 8 + BM * 4 + (BM + 1) * 4 + 2 * GROUPS * 4 + 2 * STAGES_ * 8 + 256;
   }
 };
 
@@ -61,7 +61,19 @@ csr_block_starts_kernel(const int* __restrict__ row_offsets, const int* __restri
   starts[t] = lo;
 }
 
-template <class Cfg>
+__device__ __forceinline__ float4 lds_f4(const unsigned char* p) {
+  return *reinterpret_cast<const float4*>(p);
+}
+__device__ __forceinline__ float dot4(const float4& l, const float4& r, float acc) {
+  acc = fmaf(l.x, r.x, acc);
+  acc = fmaf(l.y, r.y, acc);
+  acc = fmaf(l.z, r.z, acc);
+  return fmaf(l.w, r.w, acc);
+}
+
+// NB_LO: batches (of 4 slots) executed unconditionally -- straight-line code the scheduler can
+// software-pipeline across; the host derives it from the expected tile population minus 4 sigma.
+template <class Cfg, int NB_LO>
 __global__ void __launch_bounds__(Cfg::THREADS, 2)
 sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
                      const int* __restrict__ starts, const __grid_constant__ CUtensorMap tm_lhs,
@@ -77,8 +89,9 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
   int* const oidx = reinterpret_cast<int*>(ent + CAP);
   int* const row_start = oidx + CAP;       // [BM]   flat index of the row's first nonzero in the tile
   int* const row_off = row_start + BM;     // [BM+1] exclusive prefix of the per-row counts
+  unsigned* const fresh = reinterpret_cast<unsigned*>(row_off + BM + 1);   // [2*GROUPS] new-row bits per slot
   unsigned long long* const full = reinterpret_cast<unsigned long long*>(
-      (reinterpret_cast<uintptr_t>(row_off + BM + 1) + 7) & ~uintptr_t(7));
+      (reinterpret_cast<uintptr_t>(fresh + 2 * Cfg::GROUPS) + 7) & ~uintptr_t(7));
   unsigned long long* const empty = full + STAGES;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -137,17 +150,22 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
   const int* __restrict__ cols = a.column_indices;
   float* __restrict__ out = a.out + (size_t)rep * a.nnz;
   const int c0 = cb * bn;
-  int q = 0;  // slabs consumed so far by this CTA (ring position carries across rounds)
+  int q = 0, q_base = 0;  // slabs consumed so far by this CTA (ring position carries across rounds)
+
 
   for (int lo = 0; lo < total; lo += CAP) {
     const int cnt_round = min(CAP, total - lo);
     const int per = (cnt_round + Cfg::GROUPS - 1) / Cfg::GROUPS;  // slots in use per group (<= P)
+    const int nbatch = (per + 3) >> 2;                             // 4 slots per batch
 
     // ---- deal the round's nonzeros to (group, slot) ----
+    // slot word: (rhs row offset / 16) << 16 | (lhs row offset / 16); both < 4096, so bits 12..15
+    // are zero and `word >> 12` IS the rhs byte offset.  fresh[g] bit s: slot s starts a new row.
     for (int i = tid; i < CAP; i += Cfg::THREADS) {
       ent[i] = 0u;
       oidx[i] = -1;
     }
+    if (tid < 2 * Cfg::GROUPS) fresh[tid] = 0u;
     __syncthreads();
     for (int r = warp; r < BM; r += Cfg::THREADS / 32) {
       const int off = row_off[r], cnt = row_off[r + 1] - off, s = row_start[r];
@@ -156,16 +174,15 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
         if (el < 0 || el >= cnt_round) continue;
         const int g = el / per, slot = el - g * per;
         const unsigned col_local = (unsigned)(__ldg(cols + s + i) - c0);
-        const unsigned fresh = (i == 0 || slot == 0) ? 0x80000000u : 0u;
-        ent[g * P + slot] = (col_local * 128u) | ((unsigned)r << 23) | fresh;   // lhs offset = r*128 -> bits 16..30
+        ent[g * P + slot] = (col_local << 19) | ((unsigned)r << 3);   // (col*8) << 16 | row*8
         oidx[g * P + slot] = s + i;
+        if (i == 0 || slot == 0) atomicOr(fresh + 2 * g + (slot >> 5), 1u << (slot & 31));
       }
     }
     __syncthreads();
 
-    unsigned my[P];
-#pragma unroll
-    for (int e = 0; e < P; ++e) my[e] = ent[grp * P + e];
+    const uint4* const my4 = reinterpret_cast<const uint4*>(ent + grp * P);
+    const unsigned f_lo = fresh[2 * grp], f_hi = fresh[2 * grp + 1];
     float acc[P];
 #pragma unroll
     for (int e = 0; e < P; ++e) acc[e] = 0.f;
@@ -175,7 +192,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
       const int st = qq % STAGES, use = qq / STAGES;
       if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
       unsigned char* const dst = ring + (size_t)st * stage_bytes;
-      const int ks = qq % ksteps;
+      const int ks = (qq - q_base) % ksteps;
       mbar_arrive_expect_tx(full + st, (unsigned)stage_bytes);
       tma_load_3d(dst, &tm_lhs, ks * BK, rb * BM, rep, full + st);
       tma_load_3d(dst + BM * BK * 4, &tm_rhs, ks * BK, c0, rep, full + st);
@@ -188,32 +205,46 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
       if (tid == 0 && q + STAGES - 1 < q_end) issue(q + STAGES - 1);
       const int st = q % STAGES;
       mbar_wait(full + st, (q / STAGES) & 1);
-      const unsigned char* const sl = ring + (size_t)st * stage_bytes + sub * 16;
-      const unsigned char* const sr = sl + BM * BK * 4;
+      // Plain shared loads (not asm): the mbarrier asm statements carry memory clobbers, so the
+      // compiler keeps these between the wait and the arrive but is free to pipeline them.
+      const unsigned char* const sl = ring + (size_t)st * stage_bytes + sub * 16;  // lhs rows
+      const unsigned char* const sr = sl + BM * BK * 4;                             // rhs rows
       float4 l = make_float4(0.f, 0.f, 0.f, 0.f);
+      uint4 u = my4[0];
 #pragma unroll
-      for (int e = 0; e < P; ++e) {
-        const unsigned u = my[e];
-        if ((int)u < 0) l = *reinterpret_cast<const float4*>(sl + ((u >> 16) & 0x7fffu));
-        const float4 r = *reinterpret_cast<const float4*>(sr + (u & 0xffffu));
-        acc[e] = fmaf(l.x, r.x, acc[e]);
-        acc[e] = fmaf(l.y, r.y, acc[e]);
-        acc[e] = fmaf(l.z, r.z, acc[e]);
-        acc[e] = fmaf(l.w, r.w, acc[e]);
+      for (int b = 0; b < P / 4; ++b) {
+        if (b < NB_LO || b < nbatch) {
+          const uint4 uc = u;
+          if (b + 1 < P / 4) u = my4[(b + 1 < NB_LO || b + 1 < nbatch) ? b + 1 : 0];
+          const float4 r0 = lds_f4(sr + (uc.x >> 12)), r1 = lds_f4(sr + (uc.y >> 12));
+          const float4 r2 = lds_f4(sr + (uc.z >> 12)), r3 = lds_f4(sr + (uc.w >> 12));
+          const unsigned fw = (4 * b < 32) ? f_lo : f_hi;
+          if ((fw >> ((4 * b + 0) & 31)) & 1u) l = lds_f4(sl + ((uc.x & 0xfffu) << 4));
+          acc[4 * b + 0] = dot4(l, r0, acc[4 * b + 0]);
+          if ((fw >> ((4 * b + 1) & 31)) & 1u) l = lds_f4(sl + ((uc.y & 0xfffu) << 4));
+          acc[4 * b + 1] = dot4(l, r1, acc[4 * b + 1]);
+          if ((fw >> ((4 * b + 2) & 31)) & 1u) l = lds_f4(sl + ((uc.z & 0xfffu) << 4));
+          acc[4 * b + 2] = dot4(l, r2, acc[4 * b + 2]);
+          if ((fw >> ((4 * b + 3) & 31)) & 1u) l = lds_f4(sl + ((uc.w & 0xfffu) << 4));
+          acc[4 * b + 3] = dot4(l, r3, acc[4 * b + 3]);
+        }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty + st);
     }
+    q_base = q;
 
     // ---- reduce the 8 k-slices of every slot, one finished value per lane ----
 #pragma unroll
     for (int b = 0; b < P / 8; ++b) {
-      float v[8];
+      if (2 * b < nbatch) {
+        float v[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = acc[b * 8 + i];
-      transpose_reduce<8>(v, sub);
-      const int j = oidx[grp * P + b * 8 + sub];
-      if (j >= 0) out[j] = v[0];
+        for (int i = 0; i < 8; ++i) v[i] = acc[b * 8 + i];
+        transpose_reduce<8>(v, sub);
+        const int j = oidx[grp * P + b * 8 + sub];
+        if (j >= 0) out[j] = v[0];
+      }
     }
     __syncthreads();  // ent/oidx are rewritten by the next round
   }
@@ -240,19 +271,19 @@ inline bool sddmm_sampled_applicable(const SddmmArgs& a, int replicas) {
   return 2.0 * a.nnz * a.k * replicas >= 5.0e7;
 }
 
-template <class Cfg>
-inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream_t stream,
-                                    const StagedGuard& guard, int bn) {
+template <class Cfg, int NB_LO>
+inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_t stream,
+                                   const StagedGuard& guard, int bn) {
   const int row_blocks = ceil_div(a.m, Cfg::BM), nb = ceil_div(a.n, bn);
   const size_t smem = Cfg::smem_bytes(bn);
-  static size_t configured[64] = {0};
+  static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev >= 0 && dev < 64 && configured[dev] < smem) {
-    cudaError_t e = cudaFuncSetAttribute(sddmm_sampled_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)Cfg::smem_bytes(256));
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(sddmm_sampled_kernel<Cfg, NB_LO>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes(256));
     if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled smem attribute)");
-    configured[dev] = Cfg::smem_bytes(256);
+    configured[dev] = true;
   }
   void* ws = nullptr;
   cudaError_t e = cudaMallocAsync(&ws, (size_t)a.m * (nb + 1) * 4 + 256, stream);
@@ -269,29 +300,59 @@ inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream
     return 2;
   }
   dim3 grid(row_blocks * nb, replicas);
-  sddmm_sampled_kernel<Cfg><<<grid, Cfg::THREADS, smem, stream>>>(a, guard, nb, bn, starts, tm_lhs, tm_rhs);
+  sddmm_sampled_kernel<Cfg, NB_LO><<<grid, Cfg::THREADS, smem, stream>>>(a, guard, nb, bn, starts, tm_lhs, tm_rhs);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sampled)");
   cudaFreeAsync(ws, stream);
   return 0;
 }
 
-// Tile width from the density: the widest multiple of 16 columns (<= 256, <= n) whose expected
-// nonzero count plus three standard deviations still fits the 32*P register slots of a CTA.
 template <class Cfg>
-inline int sddmm_sampled_tile_width(const SddmmArgs& a) {
+inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream_t stream,
+                                    const StagedGuard& guard, int bn) {
+  // Batches every tile is expected to fill: (mu - 4 sigma) / 32 slots per group, 4 slots per batch.
   const double density = (double)a.nnz / ((double)a.m * (double)a.n);
-  const double cap = (double)Cfg::CAP;
-  const double mu = (2.0 * cap + 9.0 - 3.0 * sqrt(4.0 * cap + 9.0)) / 2.0;   // mu + 3 sqrt(mu) = cap
-  int bn = (int)(mu / (Cfg::BM * density)) / 16 * 16;
-  const int n16 = a.n / 16 * 16;
-  bn = bn > 256 ? 256 : bn;
-  bn = bn > n16 ? n16 : bn;
-  return bn < 16 ? 16 : bn;
+  const double mu = (double)Cfg::BM * bn * density;
+  const double lo = mu - 4.0 * sqrt(mu);
+  const int nb_lo = lo > 0 ? (int)(lo / Cfg::GROUPS) / 4 : 0;
+  if (nb_lo >= 12 && Cfg::P >= 48) return launch_sddmm_sampled_nb<Cfg, 12>(a, replicas, stream, guard, bn);
+  if (nb_lo >= 8) return launch_sddmm_sampled_nb<Cfg, 8>(a, replicas, stream, guard, bn);
+  if (nb_lo >= 4) return launch_sddmm_sampled_nb<Cfg, 4>(a, replicas, stream, guard, bn);
+  return launch_sddmm_sampled_nb<Cfg, 0>(a, replicas, stream, guard, bn);
+}
+
+// Tile width: among the multiples of 8 columns (<= 256, <= n) whose expected nonzero count plus
+// three standard deviations fits the 32*P register slots of a CTA, the one with the lowest
+// modelled time = waves of 2 CTAs per SM x per-slab cost, where the per-slab cost is the larger of
+// the shared-memory wavefronts (4 clk per slot per warp) and the operand staging traffic.
+template <class Cfg>
+inline int sddmm_sampled_tile_width(const SddmmArgs& a, int replicas) {
+  const double density = (double)a.nnz / ((double)a.m * (double)a.n);
+  const int row_blocks = ceil_div(a.m, Cfg::BM);
+  const int slots = 2 * sm_count();
+  int best = 16;
+  double best_cost = 1e300;
+  const int bn_max = a.n / 8 * 8 < 256 ? a.n / 8 * 8 : 256;
+  for (int bn = 16; bn <= bn_max; bn += 8) {
+    const double mu = (double)Cfg::BM * bn * density;
+    const double need = mu + 3.0 * sqrt(mu) + 1.0;
+    if (need > (double)Cfg::CAP && bn > 16) break;
+    const int per = (int)ceil(need / Cfg::GROUPS);
+    const int batches = (per + 3) / 4;
+    const long long tiles = (long long)row_blocks * ceil_div(a.n, bn) * replicas;
+    const double waves = (double)((tiles + slots - 1) / slots);
+    const double lsu = 64.0 * (4.0 * batches + 2.0), mem = 4.0 * (Cfg::BM + bn);
+    const double cost = waves * ((lsu > mem ? lsu : mem) + 200.0);
+    if (cost < best_cost) {
+      best_cost = cost;
+      best = bn;
+    }
+  }
+  return best;
 }
 
 // Returns 0 / an error code.  The gather kernel is launched behind it as the unsorted fallback.
 inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t stream, StagedGuard* guard_out,
-                                int bn_override = 0) {
+                                int bn_override = 0, int p_override = 0) {
   unsigned id = g_call_counter.fetch_add(1) + 1;
   if (id == 0) id = g_call_counter.fetch_add(1) + 1;
   StagedGuard guard{(int)(id % kFlagSlots), id};
@@ -299,8 +360,13 @@ inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t s
   csr_check_sorted_kernel<<<min(ceil_div(a.m, 8), 4 * sm_count()), 256, 0, stream>>>(
       a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sorted check)");
-  using Cfg = SddmmSampledCfg<48, 2>;
-  const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a);
+  if (p_override == 48) {
+    using Cfg = SddmmSampledCfg<48, 2>;
+    const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, replicas);
+    return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
+  }
+  using Cfg = SddmmSampledCfg<56, 2>;
+  const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, replicas);
   return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
 }
 

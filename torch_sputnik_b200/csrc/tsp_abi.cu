@@ -22,6 +22,7 @@ std::atomic<unsigned long long> g_launches{0};
 static std::atomic<int> g_spmm_variant{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_sddmm_bn{0};
+static std::atomic<int> g_sddmm_p{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -67,6 +68,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm") == 0) return g_spmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
+  if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
   return -1;
 }
 
@@ -156,8 +158,8 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
   // (TMA-staged operands, only the sampled products).
   const int variant = g_sddmm_variant.load();
   const double density = (double)nnz / ((double)m * (double)n);
-  const bool want_tiled = variant == 2 || (variant == 0 && density >= 0.2);
-  const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.2);
+  const bool want_tiled = variant == 2 || (variant == 0 && density >= 0.22);
+  const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.22);
   if (want_tiled && sddmm_tiled_applicable(a, replicas)) {
     StagedGuard guard;
     const int rc = launch_sddmm_tiled(a, replicas, stream, &guard);
@@ -166,7 +168,7 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
     a.guard_id = guard.call_id;
   } else if (want_sampled && sddmm_sampled_applicable(a, replicas)) {
     StagedGuard guard;
-    const int rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load());
+    const int rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load(), g_sddmm_p.load());
     if (rc != 0) return rc;
     a.guard_slot = guard.slot;
     a.guard_id = guard.call_id;
