@@ -16,6 +16,14 @@ __host__ __device__ inline unsigned pattern_addr(int p, int lane) {
     case 7: return q * 128 + s * 16;                             // each quarter reads one full 128 B row
     case 8: return (lane >> 2) * 128 + (((lane >> 2) & 7) << 4); // 8 distinct addresses, 4 lanes each
     case 9: return lane * 16;                                    // fully contiguous 512 B
+    case 10: return (lane & 3) * 128 + ((lane & 3) << 4);          // 4 distinct, strided lanes (lane & 3)
+    case 11: return ((lane >> 1) & 7) * 128 + (((lane >> 1) & 7) << 4);  // 8 distinct, adjacent pairs, halves equal
+    case 12: return (lane & 1) * 128 + ((lane & 1) << 4);          // 2 distinct, alternating lanes
+    case 13: return (lane >> 1) * 128 + (((lane >> 1) & 7) << 4);  // 16 distinct, adjacent pairs
+    case 14: return ((lane & 15) >> 2) * 128 + (((lane & 15) >> 2) << 4);  // 4 distinct (groups of 4), halves equal
+    case 15: return (lane & 7) * 16;                               // 8 distinct chunks of ONE 128 B row, quarters equal
+    case 16: return ((lane >> 2) & 1) * 128 + (((lane >> 2) & 1) << 4);    // 2 distinct, groups of 4 alternate
+    case 17: return (lane & 1) * 16 + (lane >> 4) * 128;           // 2 adjacent chunks alternating, per half
     default: return 0;
   }
 }
@@ -51,9 +59,9 @@ int main() {
   cudaFuncSetAttribute(k<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   const int iters = 4000;
-  for (int warps : {8, 16, 32})
+  for (int warps : {32})
     for (int bytes : {16, 8, 4})
-      for (int p = 0; p < 10; ++p) {
+      for (int p = 0; p < 18; ++p) {
         float ms = 0;
         for (int rep = 0; rep < 2; ++rep) {
           *cyc = 0;

@@ -95,7 +95,13 @@ sddmm_tiled_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_cta
   unsigned long long* const empty = full + STAGES;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tx = tid & 15, ty = tid >> 4;
+  // 8 x 4 threads per warp (every half-warp touches 4 distinct 16-byte chunks per operand: 2
+  // wavefronts per LDS.128), 2 x 4 warps: a warp owns 64 rows x 16 columns.
+  // Lane -> (ty, tx) = (bits 0,2,3 ; bits 1,4): every aligned lane quad then reads at most two
+  // distinct 16-byte chunks of either operand, which is what makes an LDS.128 cost 2 wavefronts
+  // instead of 4 (tools/ubench/ubench_lds.cu patterns 10-16).
+  const int ty = (lane & 1) | ((lane >> 1) & 6), tx = ((lane >> 1) & 1) | ((lane >> 3) & 2);
+  const int wr = warp >> 2, wc = warp & 3;
   const int rep = blockIdx.y;
   const int K = a.k;
   const int ksteps = (K + BK - 1) / BK;
@@ -159,18 +165,18 @@ sddmm_tiled_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_cta
       mbar_wait(full + st, (q / STAGES) & 1);
       // swizzle-128B: 16-byte chunk c of row r lives at chunk (c ^ (r & 7)); our rows are
       // i*16+ty and j*16+tx, so the XOR term is a per-thread constant.
-      const char* const sa = reinterpret_cast<const char*>(ring + st * C::kStageFloats) + ty * 128;
-      const char* const sb = reinterpret_cast<const char*>(ring + st * C::kStageFloats + BM * BK) + tx * 128;
+      const char* const sa = reinterpret_cast<const char*>(ring + st * C::kStageFloats) + (wr * 64 + ty) * 128;
+      const char* const sb = reinterpret_cast<const char*>(ring + st * C::kStageFloats + BM * BK) + (wc * 16 + tx) * 128;
 #pragma unroll
       for (int kk = 0; kk < BK / 4; ++kk) {
-        const int ka = (kk ^ (ty & 7)) << 4, kb = (kk ^ (tx & 7)) << 4;
+        const int ka = (kk ^ ty) << 4, kb0 = (kk ^ tx) << 4, kb1 = (kk ^ (4 + tx)) << 4;
         ulonglong2 bq[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          bq[j] = *reinterpret_cast<const ulonglong2*>(sb + j * 16 * 128 + kb);
+          bq[j] = *reinterpret_cast<const ulonglong2*>(sb + j * 4 * 128 + ((j & 1) ? kb1 : kb0));
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const ulonglong2 aq = *reinterpret_cast<const ulonglong2*>(sa + i * 16 * 128 + ka);
+          const ulonglong2 aq = *reinterpret_cast<const ulonglong2*>(sa + i * 8 * 128 + ka);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             fma2(acc[i][j], aq.x, bq[j].x);
@@ -189,12 +195,175 @@ sddmm_tiled_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_cta
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int rl = i * 16 + ty;
+      const int rl = wr * 64 + i * 8 + ty;
       const unsigned long long mk = rowmask[rl];
       const int base = rowbase[rl];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int cl = j * 16 + tx;
+        const int cl = wc * 16 + j * 4 + tx;
+        if ((mk >> cl) & 1ull) {
+          float lo, hi;
+          unpack2(acc[i][j], lo, hi);
+          out[base + __popcll(mk & ((1ull << cl) - 1ull))] = lo + hi;
+        }
+      }
+    }
+    __syncthreads();  // rowmask is rewritten by the next tile
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// v2 micro-kernel: 128 threads, 8 x 8 outputs per thread.
+//
+// What bounded v1 (ncu, profiles/r01_sddmm_tiled_d050_ncu_summary.txt): with a 16 x 16 thread
+// layout a warp's rhs LDS.128 touches 16 distinct rows and costs 4 shared-memory wavefronts, the
+// lhs one 2 (tools/ubench/ubench_lds.cu: an LDS.128 whose half-warps each touch <= 4 distinct
+// 16-byte chunks costs 2 wavefronts, anything wider 4), so 12 loads = 32 wavefronts fed 64 FFMA2
+// = 32 SM-cycles of FMA pipe: the LSU data pipe and the FMA pipe saturate together at ~58 %.
+// Here a warp is 8 (rows) x 4 (cols) threads -- every half-warp touches exactly 4 distinct chunks
+// for either operand -- and a thread owns 8 x 8 outputs: 16 LDS.128 (32 wavefronts) per 128 FFMA2
+// (64 SM-cycles), i.e. the LSU pipe at 50 % when the FMA pipe is full.
+struct SddmmTiled2 {
+  static constexpr int BM = 128, BN = 64, BK = 32;
+  static constexpr int STAGES = 4, THREADS = 128;   // 4 x 24 KB stages, 2 CTAs per SM
+  static constexpr int kStageFloats = (BM + BN) * BK;
+  static constexpr unsigned kStageBytes = kStageFloats * 4;
+  static constexpr size_t kSmemBytes =
+      sizeof(float) * STAGES * kStageFloats + BM * 8 + BM * 4 + 2 * STAGES * 8 + 1024;
+};
+
+__global__ void __launch_bounds__(SddmmTiled2::THREADS, 2)
+sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_cta, int col_blocks,
+                    int total_tiles, const unsigned long long* __restrict__ masks,
+                    const int* __restrict__ bases, const __grid_constant__ CUtensorMap tm_lhs,
+                    const __grid_constant__ CUtensorMap tm_rhs) {
+  using C = SddmmTiled2;
+  constexpr int BM = C::BM, BN = C::BN, BK = C::BK, STAGES = C::STAGES;
+  if (g_unsorted_flag[guard.slot] == guard.call_id) return;
+
+  extern __shared__ unsigned char smem_dyn[];
+  unsigned char* const smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+  float* const ring = reinterpret_cast<float*>(smem_raw);
+  unsigned long long* const rowmask = reinterpret_cast<unsigned long long*>(ring + STAGES * C::kStageFloats);
+  int* const rowbase = reinterpret_cast<int*>(rowmask + BM);
+  unsigned long long* const full = reinterpret_cast<unsigned long long*>(rowbase + BM);
+  unsigned long long* const empty = full + STAGES;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // 8 x 4 threads per warp; ty = lane bits 0,2,3 and tx = bits 1,4 (see v1 above)
+  const int ty = (lane & 1) | ((lane >> 1) & 6), tx = ((lane >> 1) & 1) | ((lane >> 3) & 2);
+  const int wr = warp >> 1, wc = warp & 1;          // 2 x 2 warps: 64 x 32 outputs each
+  const int rep = blockIdx.y;
+  const int ksteps = (a.k + BK - 1) / BK;
+  const int t0 = blockIdx.x * tiles_per_cta;
+  const int t1 = min(total_tiles, t0 + tiles_per_cta);
+  if (t0 >= t1) return;
+  const int Q = (t1 - t0) * ksteps;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, C::THREADS / 32);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  float* __restrict__ out = a.out + (size_t)rep * a.nnz;
+
+  auto issue = [&](int q) {   // warp 0, all lanes converge here
+    const int st = q % STAGES, use = q / STAGES;
+    if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
+    if (lane == 0) {
+      const int t = t0 + q / ksteps, ks = q % ksteps;
+      const int rb = t / col_blocks, cb = t % col_blocks;
+      float* const sa = ring + st * C::kStageFloats;
+      mbar_arrive_expect_tx(full + st, C::kStageBytes);
+      tma_load_3d(sa, &tm_lhs, ks * BK, rb * BM, rep, full + st);
+      tma_load_3d(sa + BM * BK, &tm_rhs, ks * BK, cb * BN, rep, full + st);
+    }
+    __syncwarp();
+  };
+  // Prefetch distance STAGES-2: the slot refilled at step q was consumed at step q-2, so the
+  // producer warp does not have to wait for the slowest warp of the step it just left.
+  constexpr int AHEAD = STAGES - 2;
+  if (warp == 0)
+    for (int q = 0; q < min(Q, AHEAD); ++q) issue(q);
+
+  // Per-thread byte offsets inside a stage.  Rows i*8+ty have (row & 7) == ty; columns j*4+tx have
+  // (col & 7) == (j & 1)*4 + tx: the swizzle XOR terms are per-thread constants.
+  const int a_off = (wr * 64 + ty) * 128;
+  const int b_off = BM * 128 + (wc * 32 + tx) * 128;
+  const int xa = ty, xb0 = tx, xb1 = 4 + tx;
+
+  int q = 0;
+  for (int t = t0; t < t1; ++t) {
+    const int rb = t / col_blocks, cb = t % col_blocks;
+    unsigned long long my_mask = 0ull;
+    int my_base = 0;
+    if (rb * BM + tid < a.m) {   // THREADS == BM
+      const size_t e = (size_t)(rb * BM + tid) * col_blocks + cb;
+      my_mask = __ldg(masks + e);
+      my_base = __ldg(bases + e);
+    }
+
+    unsigned long long acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0ull;
+
+    for (int ks = 0; ks < ksteps; ++ks, ++q) {
+      if (warp == 0 && q + AHEAD < Q) issue(q + AHEAD);
+      const int st = q % STAGES;
+      mbar_wait(full + st, (q / STAGES) & 1);
+      const char* const sbase = reinterpret_cast<const char*>(ring + st * C::kStageFloats);
+      const char* const sa = sbase + a_off;
+      const char* const sb = sbase + b_off;
+      // One k-pair (even k, odd k) per step: 8 + 8 LDS.64 feed 64 FFMA2.  Narrow loads keep the
+      // operand registers at 16 (+16 for the next step's lhs, requested one step ahead) next to
+      // the 128 accumulator registers.
+      auto a_addr = [&](int i, int kp) { return sa + i * 8 * 128 + (((kp >> 1) ^ xa) << 4) + (kp & 1) * 8; };
+      auto step = [&](const unsigned long long (&av)[8], int kp) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const unsigned long long bq = *reinterpret_cast<const unsigned long long*>(
+              sb + j * 4 * 128 + (((kp >> 1) ^ ((j & 1) ? xb1 : xb0)) << 4) + (kp & 1) * 8);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) fma2(acc[i][j], av[i], bq);
+        }
+      };
+      unsigned long long a0[8], a1[8];   // ping-pong lhs registers, each requested one step ahead
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a0[i] = *reinterpret_cast<const unsigned long long*>(a_addr(i, 0));
+#pragma unroll
+      for (int kp = 0; kp < BK / 2; kp += 2) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a1[i] = *reinterpret_cast<const unsigned long long*>(a_addr(i, kp + 1));
+        step(a0, kp);
+        if (kp + 2 < BK / 2) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) a0[i] = *reinterpret_cast<const unsigned long long*>(a_addr(i, kp + 2));
+        }
+        step(a1, kp + 1);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty + st);
+    }
+
+    rowmask[tid] = my_mask;
+    rowbase[tid] = my_base;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int rl = wr * 64 + i * 8 + ty;
+      const unsigned long long mk = rowmask[rl];
+      const int base = rowbase[rl];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int cl = wc * 32 + j * 4 + tx;
         if ((mk >> cl) & 1ull) {
           float lo, hi;
           unpack2(acc[i][j], lo, hi);
@@ -247,7 +416,8 @@ inline bool sddmm_tiled_applicable(const SddmmArgs& a, int replicas) {
 }
 
 // Returns 0 / an error code.  The gather kernel is launched behind it as the unsorted fallback.
-inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t stream, StagedGuard* guard_out) {
+inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t stream, StagedGuard* guard_out,
+                             bool v1 = false) {
   using C = SddmmTiled;
   unsigned id = g_call_counter.fetch_add(1) + 1;
   if (id == 0) id = g_call_counter.fetch_add(1) + 1;
@@ -259,6 +429,9 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
   if (dev >= 0 && dev < 64 && !configured[dev]) {
     cudaError_t e = cudaFuncSetAttribute(sddmm_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)C::kSmemBytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(sddmm_tiled2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)SddmmTiled2::kSmemBytes);
     if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (tiled smem attribute)");
     configured[dev] = true;
   }
@@ -288,8 +461,12 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
     return 2;
   }
   dim3 grid(ctas, replicas);
-  sddmm_tiled_kernel<<<grid, C::THREADS, C::kSmemBytes, stream>>>(a, guard, per_cta, col_blocks,
-                                                                  (int)total, masks, bases, tm_lhs, tm_rhs);
+  if (v1)
+    sddmm_tiled_kernel<<<grid, C::THREADS, C::kSmemBytes, stream>>>(a, guard, per_cta, col_blocks,
+                                                                    (int)total, masks, bases, tm_lhs, tm_rhs);
+  else
+    sddmm_tiled2_kernel<<<grid, SddmmTiled2::THREADS, SddmmTiled2::kSmemBytes, stream>>>(
+        a, guard, per_cta, col_blocks, (int)total, masks, bases, tm_lhs, tm_rhs);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (tiled)");
   cudaFreeAsync(ws, stream);
   return 0;

@@ -158,11 +158,11 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
   // (TMA-staged operands, only the sampled products).
   const int variant = g_sddmm_variant.load();
   const double density = (double)nnz / ((double)m * (double)n);
-  const bool want_tiled = variant == 2 || (variant == 0 && density >= 0.22);
+  const bool want_tiled = variant == 2 || variant == 4 || (variant == 0 && density >= 0.22);   // 4 = tiled v1
   const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.22);
   if (want_tiled && sddmm_tiled_applicable(a, replicas)) {
     StagedGuard guard;
-    const int rc = launch_sddmm_tiled(a, replicas, stream, &guard);
+    const int rc = launch_sddmm_tiled(a, replicas, stream, &guard, variant == 4);
     if (rc != 0) return rc;
     a.guard_slot = guard.slot;   // the gather launch below becomes the unsorted-columns fallback
     a.guard_id = guard.call_id;
