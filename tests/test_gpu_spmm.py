@@ -235,3 +235,28 @@ def test_spmm_shim_rejects_bad_arguments(ops, dev):
         ops.spmm(16, 17, v, ri, ro, ci, bd)
     with pytest.raises(RuntimeError):
         ops.spmm(16, 16, v, ri, ro[:-1], ci, bd)
+
+
+@pytest.mark.parametrize("warps", [4, 16, 32])
+@pytest.mark.parametrize("m,k,n,density,reps", [
+    (300, 1024, 64, 0.1, 1), (4096, 4096, 64, 0.1, 2), (130, 700, 16, 0.3, 3), (257, 520, 128, 0.2, 1),
+    (129, 2048, 100, 0.06, 2), (1000, 1000, 33, 0.15, 1)])
+def test_spmm_narrow_operand_wide_ctas(ops, dev, m, k, n, density, reps, warps):
+    """Gather variant at the attention P @ V shapes with every CTA width: ragged m / k / n, replicas."""
+    a = random_csr(m, k, density, seed=m + k + n, values="pm1")
+    lead = (reps,) if reps > 1 else ()
+    b = dense_operand(lead + (k, n), 41, "pm1")
+    v, ri, ro, ci = to_dev(a, dev)
+    vals = torch.from_numpy(np.stack([a.values * (r + 1) for r in range(reps)])).to(dev) if reps > 1 else v
+    prev, prevw = ops.set_variant("spmm", 1), ops.set_variant("spmm_warps", warps)
+    try:
+        got = ops.spmm(m, k, vals, ri, ro, ci, torch.from_numpy(b).to(dev)).cpu().numpy()
+    finally:
+        ops.set_variant("spmm", prev)
+        ops.set_variant("spmm_warps", prevw)
+    for r in range(reps):
+        vr = a.values * (r + 1) if reps > 1 else a.values
+        br = b[r] if reps > 1 else b
+        ref = oracle.spmm(m, k, vr, a.row_offsets, a.column_indices, br)
+        scale = oracle.spmm_abs(m, k, vr, a.row_offsets, a.column_indices, br)
+        assert_close_fwd(got[r] if reps > 1 else got, ref, scale, what=f"narrow {m}x{k}x{n} replica {r}")

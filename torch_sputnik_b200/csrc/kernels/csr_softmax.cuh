@@ -50,8 +50,10 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < REG; ++i) {
-      v[i] = expf(v[i] - mx);  // expf(-inf) == 0 for the padding lanes
-      sum += v[i];
+      if (32 * i < len) {        // warp-uniform: register slots past the row do no work
+        v[i] = expf(v[i] - mx);  // expf(-inf) == 0 for the padding lanes
+        sum += v[i];
+      }
     }
     sum = warp_sum(sum);
     const float inv = 1.0f / sum;

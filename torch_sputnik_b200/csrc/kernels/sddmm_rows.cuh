@@ -1,0 +1,122 @@
+// sddmm_rows.cuh -- SDDMM, variant 5 ("rows"): the path for a SHORT inner dimension
+// (k = 32, 64, 96 or 128: attention scores, out = sample(Q @ K^T) with head_dim 64).
+//
+// out[j] = <lhs[row_of(j), :], rhs[col(j), :]>.  With k = 64 an rhs row is 256 bytes; the general
+// gather kernel (variant 1) then spends ~25 instructions per nonzero on bookkeeping (two shuffles
+// and a 64-bit address per 4 FMAs, a 16-lane butterfly per 16 nonzeros) and is issue- and
+// latency-bound (profiles/r01_sddmm_gather_c4_ncu_summary.txt).  Here:
+//
+//  * one warp owns one mask row and keeps its lhs k-slices in registers for the whole row: lane
+//    `sub` of every quarter-warp holds the 16-byte chunks sub, sub+8, ... of lhs[row, :];
+//  * the row's nonzeros are taken 32 at a time (one coalesced load of column indices); in step g
+//    quarter q works on nonzero 4g+q: each lane reads the same chunks of rhs[col, :], so a
+//    quarter-warp LDG.128 is one contiguous 128-byte request, and the address is ONE wide
+//    multiply-add (column x row-vectors onto the lane's base pointer, IMAD.WIDE.U32);
+//  * a transposing butterfly over the 8 lanes of a quarter (7 shuffles per 32 nonzeros instead
+//    of 3 per nonzero) leaves nonzero 4*sub+q in lane (q, sub); the 32 results go out in one
+//    128-byte segment;
+//  * a CTA is 16 consecutive rows: with ascending columns they sweep the rhs rows in near
+//    lockstep, so the rows they share are L1 hits ("implicit banding").
+//
+// Arithmetic: per lane fp32 FMA in ascending k inside its chunks, then a fp32 tree over the 8
+// lanes -- the shape of the reference's (all_reduce.h:61-80), a different association.
+// Works for any column order (no sortedness assumption).  Needs k % 32 == 0, k <= 128,
+// 16-byte aligned operands and n * k * 4 < 2^31.
+#pragma once
+#include "sddmm_gather.cuh"
+
+namespace tsp {
+
+template <int KC, int WARPS>   // k = 32 * KC
+__global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgs a) {
+  constexpr int K = 32 * KC;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * WARPS + warp;
+  if (row >= a.m) return;
+  const int rep = blockIdx.y;
+  const int q = lane >> 3, sub = lane & 7;
+
+  const int beg = __ldg(a.row_offsets + row), end = __ldg(a.row_offsets + row + 1);
+  if (beg >= end) return;
+  const int* __restrict__ cols = a.column_indices;
+  float* __restrict__ out = a.out + (size_t)rep * a.nnz;
+  // this lane's chunk `sub` of rhs row 0 (float4 units); chunk cc of row c is at + c * (K/4) + cc * 8
+  const float4* const rbase = reinterpret_cast<const float4*>(a.rhs + (size_t)rep * a.n * K) + sub;
+  const float4* const lrow = reinterpret_cast<const float4*>(a.lhs + ((size_t)rep * a.m + row) * K) + sub;
+  float4 lv[KC];
+#pragma unroll
+  for (int cc = 0; cc < KC; ++cc) lv[cc] = __ldg(lrow + cc * 8);
+
+  for (int p = beg; p < end; p += 32) {
+    const int cnt = min(32, end - p);
+    // rhs row offset of nonzero p + lane in float4 units (row 0 for the lanes past the row's end:
+    // a valid address, the result is never stored)
+    const unsigned myoff = lane < cnt ? (unsigned)__ldg(cols + p + lane) * (unsigned)(K / 4) : 0u;
+    float acc[8];
+    if (cnt == 32) {
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        const unsigned o = __shfl_sync(kFullMask, myoff, 4 * g + q);
+        float s = 0.f;
+#pragma unroll
+        for (int cc = 0; cc < KC; ++cc) {
+          const float4 x = __ldg(rbase + o + cc * 8);
+          s = fmaf(lv[cc].x, x.x, s);
+          s = fmaf(lv[cc].y, x.y, s);
+          s = fmaf(lv[cc].z, x.z, s);
+          s = fmaf(lv[cc].w, x.w, s);
+        }
+        acc[g] = s;
+      }
+    } else {
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        acc[g] = 0.f;
+        if (4 * g < cnt) {   // warp-uniform
+          const unsigned o = __shfl_sync(kFullMask, myoff, 4 * g + q);
+          float s = 0.f;
+#pragma unroll
+          for (int cc = 0; cc < KC; ++cc) {
+            const float4 x = __ldg(rbase + o + cc * 8);
+            s = fmaf(lv[cc].x, x.x, s);
+            s = fmaf(lv[cc].y, x.y, s);
+            s = fmaf(lv[cc].z, x.z, s);
+            s = fmaf(lv[cc].w, x.w, s);
+          }
+          acc[g] = s;
+        }
+      }
+    }
+    transpose_reduce<8>(acc, sub);   // lane (q, sub) now holds nonzero 4 * sub + q of the batch
+    const int j = 4 * sub + q;
+    if (j < cnt) out[p + j] = acc[0];
+  }
+}
+
+inline bool sddmm_rows_applicable(const SddmmArgs& a) {
+  if (a.k % 32 != 0 || a.k > 128 || a.k < 32) return false;
+  if (!aligned16(a.lhs) || !aligned16(a.rhs)) return false;
+  return (unsigned long long)a.n * (unsigned long long)a.k * 4ull < (1ull << 31);
+}
+
+extern std::atomic<int> g_sddmm_warps;   // benchmark knob "sddmm_warps": rows per CTA (0 = default 16)
+
+template <int KC>
+inline void launch_sddmm_rows_kc(const SddmmArgs& a, int replicas, cudaStream_t stream) {
+  const int w = g_sddmm_warps.load();
+  if (w == 4) sddmm_rows_kernel<KC, 4><<<dim3(ceil_div(a.m, 4), replicas), 128, 0, stream>>>(a);
+  else if (w == 8) sddmm_rows_kernel<KC, 8><<<dim3(ceil_div(a.m, 8), replicas), 256, 0, stream>>>(a);
+  else if (w == 32) sddmm_rows_kernel<KC, 32><<<dim3(ceil_div(a.m, 32), replicas), 1024, 0, stream>>>(a);
+  else sddmm_rows_kernel<KC, 16><<<dim3(ceil_div(a.m, 16), replicas), 512, 0, stream>>>(a);
+}
+
+inline void launch_sddmm_rows(const SddmmArgs& a, int replicas, cudaStream_t stream) {
+  switch (a.k / 32) {
+    case 1: launch_sddmm_rows_kc<1>(a, replicas, stream); break;
+    case 2: launch_sddmm_rows_kc<2>(a, replicas, stream); break;
+    case 3: launch_sddmm_rows_kc<3>(a, replicas, stream); break;
+    default: launch_sddmm_rows_kc<4>(a, replicas, stream); break;
+  }
+}
+
+}  // namespace tsp

@@ -77,7 +77,12 @@ __device__ __forceinline__ void store_vec(float* p, const float (&src)[VEC]) {
   }
 }
 
-template <int VEC, int U, int WARPS>
+// OFF32: the staged pair carries the operand row's offset in VECTOR units (col * n / VEC; n % VEC
+// == 0 on the vector paths, fits 32 bits when k * n * 4 < 2^31, checked on the host) instead of
+// the column, so a gather address is ONE wide multiply-add onto the lane's own 64-bit base
+// (IMAD.WIDE.U32) instead of a 64-bit multiply + adds per load -- the gather loop was
+// issue-bound on that arithmetic (profiles/r01_spmm_gather_c4_ncu_summary.txt).
+template <int VEC, int U, int WARPS, bool OFF32>
 __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs a) {
   __shared__ __align__(16) int2 s_pairs[WARPS][32];
   if (a.guard_id != 0 && g_unsorted_flag[a.guard_slot] != a.guard_id) return;
@@ -92,6 +97,11 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
   const int n = a.n;
   const int n0 = blockIdx.y * (32 * VEC * U) + lane * VEC;
   const float* __restrict__ dense = a.dense + (size_t)rep * a.k * n;
+  using V = typename VecT<VEC>::type;
+  const V* lane_base[U];   // this lane's slice of operand row 0, per column tile
+#pragma unroll
+  for (int u = 0; u < U; ++u) lane_base[u] = reinterpret_cast<const V*>(dense + n0 + u * 32 * VEC);
+  const unsigned row_vecs = (unsigned)n / VEC;
   const float* __restrict__ vals = a.values + (size_t)rep * a.values_stride;
   const int* __restrict__ cols = a.column_indices;
 
@@ -115,6 +125,7 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
     if (lane < cnt) {
       p.x = __float_as_int(__ldg(vals + base + lane));
       p.y = __ldg(cols + base + lane);
+      if (OFF32) p.y = (int)((unsigned)p.y * row_vecs);
     }
     __syncwarp();
     sp[lane] = p;
@@ -132,7 +143,12 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
       for (int t = 0; t < 4; ++t)
 #pragma unroll
         for (int u = 0; u < U; ++u)
-          if (ok[u]) load_vec<VEC>(b[t][u], dense + (size_t)ac[t] * n + n0 + u * 32 * VEC);
+          if (ok[u]) {
+            if (OFF32)
+              load_vec<VEC>(b[t][u], reinterpret_cast<const float*>(lane_base[u] + (unsigned)ac[t]));
+            else
+              load_vec<VEC>(b[t][u], dense + (size_t)ac[t] * n + n0 + u * 32 * VEC);
+          }
 #pragma unroll
       for (int t = 0; t < 4; ++t)
 #pragma unroll
@@ -148,7 +164,10 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
       for (int u = 0; u < U; ++u)
         if (ok[u]) {
           float b[VEC];
-          load_vec<VEC>(b, dense + (size_t)q.y * n + n0 + u * 32 * VEC);
+          if (OFF32)
+            load_vec<VEC>(b, reinterpret_cast<const float*>(lane_base[u] + (unsigned)q.y));
+          else
+            load_vec<VEC>(b, dense + (size_t)q.y * n + n0 + u * 32 * VEC);
 #pragma unroll
           for (int v = 0; v < VEC; ++v) acc[u][v] = fmaf(av, b[v], acc[u][v]);
         }
@@ -169,11 +188,30 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
     }
 }
 
+// Rows per CTA (benchmark knob "spmm_warps"; 0 = default).  With a narrow dense operand the rows
+// of a CTA walk the column space in near lockstep, so a wide CTA keeps the operand rows they
+// share in L1 ("implicit banding").
+extern std::atomic<int> g_spmm_warps;
+
+template <int VEC, int U, int WARPS>
+inline void launch_spmm_gather_w(const SpmmArgs& a, int replicas, cudaStream_t stream) {
+  dim3 grid(ceil_div(a.m, WARPS), ceil_div(a.n, 32 * VEC * U), replicas);
+  if ((unsigned long long)a.k * (unsigned long long)a.n * 4ull < (1ull << 31))
+    spmm_gather_kernel<VEC, U, WARPS, true><<<grid, WARPS * 32, 0, stream>>>(a);
+  else
+    spmm_gather_kernel<VEC, U, WARPS, false><<<grid, WARPS * 32, 0, stream>>>(a);
+}
+
 template <int VEC, int U>
 inline void launch_spmm_gather(const SpmmArgs& a, int replicas, cudaStream_t stream) {
-  constexpr int WARPS = 4;
-  dim3 grid(ceil_div(a.m, WARPS), ceil_div(a.n, 32 * VEC * U), replicas);
-  spmm_gather_kernel<VEC, U, WARPS><<<grid, WARPS * 32, 0, stream>>>(a);
+  int w = g_spmm_warps.load();
+  if (w == 0) w = (a.n <= 32 * VEC * U && a.n <= 128 && a.k >= 1024) ? 16 : 4;
+  switch (w) {
+    case 8: launch_spmm_gather_w<VEC, U, 8>(a, replicas, stream); break;
+    case 16: launch_spmm_gather_w<VEC, U, 16>(a, replicas, stream); break;
+    case 32: launch_spmm_gather_w<VEC, U, 32>(a, replicas, stream); break;
+    default: launch_spmm_gather_w<VEC, U, 4>(a, replicas, stream); break;
+  }
 }
 
 }  // namespace tsp

@@ -3,6 +3,7 @@
 // any other host (ctypes, a C++ harness) call exactly these symbols.
 #include "../../include/tsp.h"
 
+#include <cmath>
 #include <cstring>
 #include <mutex>
 
@@ -14,12 +15,15 @@
 #include "kernels/spmm_staged.cuh"
 #include "kernels/sddmm_staged.cuh"
 #include "kernels/sddmm_sampled.cuh"
+#include "kernels/sddmm_rows.cuh"
 
 namespace tsp {
 
 static thread_local char t_error[512] = "";
 std::atomic<unsigned long long> g_launches{0};
 static std::atomic<int> g_spmm_variant{0};
+std::atomic<int> g_spmm_warps{0};
+std::atomic<int> g_sddmm_warps{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_sddmm_bn{0};
 static std::atomic<int> g_sddmm_p{0};
@@ -66,6 +70,8 @@ unsigned long long tsp_launch_count(void) { return g_launches.load(); }
 
 int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm") == 0) return g_spmm_variant.exchange(variant);
+  if (op && strcmp(op, "spmm_warps") == 0) return g_spmm_warps.exchange(variant);
+  if (op && strcmp(op, "sddmm_warps") == 0) return g_sddmm_warps.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
@@ -105,16 +111,15 @@ int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
 
   // variant: 0 = heuristic, 1 = gather, 2 = staged (rows per group from density), 3 = staged with
   // 4-row groups, 4 = staged with 8-row groups.
-  if (variant != 1 && spmm_staged_applicable(a, replicas)) {
-    const double density = (double)nnz / ((double)m * (double)k);
+  const double density = (double)nnz / ((double)m * (double)k);
+  const bool staged_ok = variant != 1 && spmm_staged_applicable(a, replicas) &&
+                         (variant != 0 || density >= 0.22);
+  if (staged_ok) {
     // Below ~22 % density (measured crossover on B200, profiles/) rows of a group share almost no columns, merging cannot raise the FMA
     // per shared-memory wavefront ratio, and the L1/L2 gather kernel has less fixed cost per slab.
-    if (variant != 0 || density >= 0.22) {
-      const int rc = launch_spmm_staged(a, replicas, stream, variant == 3 ? 4 : (variant == 4 ? 8 : 0));
-      if (rc >= 0) return rc;  // < 0: staged path declined, use the gather kernel
-    }
+    const int rc = launch_spmm_staged(a, replicas, stream, variant == 3 ? 4 : (variant == 4 ? 8 : 0));
+    if (rc >= 0) return rc;  // < 0: staged path declined, use the gather kernel
   }
-
   if (vec4_ok && n > 128) {
     launch_spmm_gather<4, 2>(a, replicas, stream);
   } else if (vec4_ok && n > 64) {
@@ -155,11 +160,18 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
   a.out = out;
 
   // variant: 0 = heuristic, 1 = gather, 2 = tiled (dense register tiles, sampled), 3 = sampled
-  // (TMA-staged operands, only the sampled products).
+  // (TMA-staged operands, only the sampled products), 4 = tiled v1,
+  // 5 = rows (k <= 128).
   const int variant = g_sddmm_variant.load();
   const double density = (double)nnz / ((double)m * (double)n);
   const bool want_tiled = variant == 2 || variant == 4 || (variant == 0 && density >= 0.22);   // 4 = tiled v1
   const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.22);
+  // 5 = rows (short inner dimension, k <= 128): no sortedness requirement, no fallback needed.
+  if ((variant == 5 || (variant == 0 && (k < 128 || density < 0.22))) && sddmm_rows_applicable(a)) {
+    launch_sddmm_rows(a, replicas, stream);
+    TSP_CHECK_LAUNCH("tsp_sddmm_f32 (rows)");
+    return TSP_OK;
+  }
   if (want_tiled && sddmm_tiled_applicable(a, replicas)) {
     StagedGuard guard;
     const int rc = launch_sddmm_tiled(a, replicas, stream, &guard, variant == 4);
@@ -190,8 +202,10 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
 
 // --------------------------------------------------------------------------------- softmax
 static int pick_softmax_reg(int m, int nnz) {
-  const long long avg = m > 0 ? (long long)nnz / m : 0;
-  const long long want = avg + avg / 4 + 32;
+  // Registers per lane so that (nearly) every row fits: mean row length + 4.5 sigma of a binomial
+  // row population; longer rows take the three-pass path of the same kernel.
+  const double avg = m > 0 ? (double)nnz / m : 0.0;
+  const double want = avg + 4.5 * sqrt(avg) + 1.0;
   if (want <= 32 * 4) return 4;
   if (want <= 32 * 8) return 8;
   if (want <= 32 * 16) return 16;
