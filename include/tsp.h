@@ -80,6 +80,18 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas,
                   float* out, void* stream);
 
 /*
+ * SDDMM summed over replicas:  out[j] = sum_r dot(lhs[r, row_of(j), :], rhs[r, column_indices[j], :])
+ *   out is ONE [nnz] vector.  This is the weight gradient of a sparse linear layer: the reference
+ *   computes sddmm into [replicas, nnz] (modules/sparse_linear.py:44) and lets autograd sum over
+ *   the batch dimension; here the replica loop is folded into the kernel's k loop, so the
+ *   [replicas, nnz] intermediate never exists.  Arguments as tsp_sddmm_f32.
+ */
+int tsp_sddmm_reduce_f32(int m, int k, int n, int nnz, int replicas,
+                         const int* row_indices, const int* row_offsets,
+                         const int* column_indices, const float* lhs, const float* rhs,
+                         float* out, void* stream);
+
+/*
  * CSR softmax: for every row i and replica r, over seg = [row_offsets[i], row_offsets[i+1]):
  *   out[r, seg] = exp(scale*x - max(scale*x)) / sum(exp(scale*x - max(scale*x))),  x = values[r, seg]
  *   The reference has no scale (scale = 1.0f); scale folds the caller-side 1/sqrt(d)

@@ -261,3 +261,37 @@ def test_sddmm_rows_empty_rows_and_unsorted(ops, dev):
         check_sddmm(ops, dev, a, dense_operand((m, k), 53, "pm1"), dense_operand((n, k), 54, "pm1"), "rows skew")
     finally:
         ops.set_variant("sddmm", prev)
+
+
+@pytest.mark.parametrize("m,n,k,density,reps", [
+    (256, 320, 512, 0.1, 4),      # sampled kernel, replica loop folded into the k loop
+    (256, 320, 512, 0.5, 3),      # tiled kernel
+    (130, 70, 96, 0.3, 5),        # neither staged kernel applies: scratch + reduce
+    (300, 513, 260, 0.05, 2), (128, 128, 256, 0.1, 1)])
+def test_sddmm_reduce_sums_over_replicas(ops, dev, m, n, k, density, reps):
+    """sddmm_reduce == sddmm(...).sum(0): the sparse-linear weight gradient (modules/sparse_linear.py:44
+    + autograd's broadcast sum) without the [R, nnz] intermediate."""
+    a = random_csr(m, n, density, seed=m + n + k + reps, values="pm1")
+    lhs, rhs = dense_operand((reps, m, k), 61, "pm1"), dense_operand((reps, n, k), 62, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    got = ops.sddmm_reduce(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev))
+    assert tuple(got.shape) == (a.nnz,)
+    ref = oracle.sddmm(m, n, a.row_offsets, a.column_indices, lhs, rhs).astype(np.float64).reshape(reps, -1).sum(0)
+    scale = sum(oracle.sddmm_abs(m, n, a.row_offsets, a.column_indices, lhs[r], rhs[r]).astype(np.float64)
+                for r in range(reps))
+    assert_close_fwd(got.cpu().numpy(), ref, scale, what=f"sddmm_reduce {m}x{n}x{k} R={reps}")
+
+
+def test_sddmm_reduce_unsorted_columns(ops, dev):
+    a = random_csr(256, 320, 0.15, seed=71, values="pm1")
+    rng = np.random.default_rng(4)
+    for i in range(a.m):
+        s, e = a.row_offsets[i], a.row_offsets[i + 1]
+        a.column_indices[s:e] = a.column_indices[s:e][rng.permutation(e - s)]
+    lhs, rhs = dense_operand((3, 256, 512), 63, "pm1"), dense_operand((3, 320, 512), 64, "pm1")
+    _, ri, ro, ci = to_dev(a, dev)
+    got = ops.sddmm_reduce(256, 320, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev))
+    ref = oracle.sddmm(256, 320, a.row_offsets, a.column_indices, lhs, rhs).astype(np.float64).sum(0)
+    scale = sum(oracle.sddmm_abs(256, 320, a.row_offsets, a.column_indices, lhs[r], rhs[r]).astype(np.float64)
+                for r in range(3))
+    assert_close_fwd(got.cpu().numpy(), ref, scale, what="sddmm_reduce unsorted")

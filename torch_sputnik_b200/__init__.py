@@ -44,6 +44,7 @@ sparse_softmax = torch_sputnik.sparse_softmax
 csr_transpose = torch_sputnik.csr_transpose
 spmm_bias_relu = torch_sputnik.spmm_bias_relu
 spmm_bias = torch_sputnik.spmm_bias
+sddmm_reduce = torch_sputnik.sddmm_reduce
 sparse_softmax_scaled = torch_sputnik.sparse_softmax_scaled
 sparse_softmax_backward = torch_sputnik.sparse_softmax_backward
 csr_transpose_with_perm = torch_sputnik.csr_transpose_with_perm
@@ -53,6 +54,6 @@ launch_count = torch_sputnik.launch_count
 
 __all__ = [
     "torch_sputnik", "spmm", "left_spmm", "sddmm", "sparse_softmax", "csr_transpose",
-    "spmm_bias_relu", "spmm_bias", "sparse_softmax_scaled", "sparse_softmax_backward",
+    "spmm_bias_relu", "spmm_bias", "sddmm_reduce", "sparse_softmax_scaled", "sparse_softmax_backward",
     "csr_transpose_with_perm", "permute_values", "set_variant", "launch_count",
 ]

@@ -28,6 +28,10 @@ struct SddmmArgs {
   // if g_unsorted_flag[guard_slot] == guard_id.
   int guard_slot = 0;
   unsigned guard_id = 0;
+  // reduce_reps > 0: out is ONE [nnz] vector holding the sum over that many replicas (the
+  // weight gradient of a sparse linear layer); the staged kernels fold the replica loop into
+  // their k loop, grid.y is 1.
+  int reduce_reps = 0;
 };
 
 // Row containing flat nonzero j: largest i with row_offsets[i] <= j (skips empty rows).
@@ -130,6 +134,19 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   transpose_reduce<LPN>(acc, lane);
   const int j = j0 + grp * NPG + sub;
   if (j < a.nnz) a.out[(size_t)rep * a.nnz + j] = acc[0];
+}
+
+// out[j] = sum_r scratch[r, j] (ascending r).  guard_id != 0: runs only as the unsorted-columns
+// fallback of a staged reduce launch (the staged kernel has written out[] itself otherwise).
+__global__ void __launch_bounds__(256)
+reduce_replicas_kernel(const float* __restrict__ scratch, int nnz, int replicas, float* __restrict__ out,
+                       int guard_slot, unsigned guard_id) {
+  if (guard_id != 0 && g_unsorted_flag[guard_slot] != guard_id) return;
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= nnz) return;
+  float s = 0.f;
+  for (int r = 0; r < replicas; ++r) s += ld_stream_f(scratch + (size_t)r * nnz + j);
+  out[j] = s;
 }
 
 template <int VEC, int LPN>

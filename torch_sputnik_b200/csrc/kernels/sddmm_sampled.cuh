@@ -98,7 +98,8 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
   const int grp = tid >> 3, sub = tid & 7;
   const int rb = blockIdx.x / nb, cb = blockIdx.x % nb;
   const int rep = blockIdx.y;
-  const int ksteps = (a.k + BK - 1) / BK;
+  const int ksteps1 = (a.k + BK - 1) / BK;                                   // k-slabs of one replica
+  const int ksteps = a.reduce_reps > 0 ? ksteps1 * a.reduce_reps : ksteps1;   // slabs per tile round
 
   if (tid == 0) {
 #pragma unroll
@@ -192,10 +193,11 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
       const int st = qq % STAGES, use = qq / STAGES;
       if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
       unsigned char* const dst = ring + (size_t)st * stage_bytes;
-      const int ks = (qq - q_base) % ksteps;
+      const int kq = (qq - q_base) % ksteps;
+      const int ks = kq % ksteps1, rr = a.reduce_reps > 0 ? kq / ksteps1 : rep;
       mbar_arrive_expect_tx(full + st, (unsigned)stage_bytes);
-      tma_load_3d(dst, &tm_lhs, ks * BK, rb * BM, rep, full + st);
-      tma_load_3d(dst + BM * BK * 4, &tm_rhs, ks * BK, c0, rep, full + st);
+      tma_load_3d(dst, &tm_lhs, ks * BK, rb * BM, rr, full + st);
+      tma_load_3d(dst + BM * BK * 4, &tm_rhs, ks * BK, c0, rr, full + st);
     };
     const int q_end = q + ksteps;
     if (tid == 0)
@@ -299,7 +301,7 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
     set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  dim3 grid(row_blocks * nb, replicas);
+  dim3 grid(row_blocks * nb, a.reduce_reps > 0 ? 1 : replicas);
   sddmm_sampled_kernel<Cfg, NB_LO><<<grid, Cfg::THREADS, smem, stream>>>(a, guard, nb, bn, starts, tm_lhs, tm_rhs);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sampled)");
   cudaFreeAsync(ws, stream);
@@ -360,13 +362,14 @@ inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t s
   csr_check_sorted_kernel<<<min(ceil_div(a.m, 8), 4 * sm_count()), 256, 0, stream>>>(
       a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sorted check)");
+  const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;   // tiles are spread over this many grid.y slices
   if (p_override == 48) {
     using Cfg = SddmmSampledCfg<48, 2>;
-    const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, replicas);
+    const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, grid_reps);
     return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
   }
   using Cfg = SddmmSampledCfg<56, 2>;
-  const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, replicas);
+  const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, grid_reps);
   return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
 }
 

@@ -255,7 +255,8 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
   const int ty = (lane & 1) | ((lane >> 1) & 6), tx = ((lane >> 1) & 1) | ((lane >> 3) & 2);
   const int wr = warp >> 1, wc = warp & 1;          // 2 x 2 warps: 64 x 32 outputs each
   const int rep = blockIdx.y;
-  const int ksteps = (a.k + BK - 1) / BK;
+  const int ksteps1 = (a.k + BK - 1) / BK;                                   // k-steps of one replica
+  const int ksteps = a.reduce_reps > 0 ? ksteps1 * a.reduce_reps : ksteps1;   // k-steps per tile
   const int t0 = blockIdx.x * tiles_per_cta;
   const int t1 = min(total_tiles, t0 + tiles_per_cta);
   if (t0 >= t1) return;
@@ -277,12 +278,13 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
     const int st = q % STAGES, use = q / STAGES;
     if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
     if (lane == 0) {
-      const int t = t0 + q / ksteps, ks = q % ksteps;
+      const int t = t0 + q / ksteps, kq = q % ksteps;
+      const int ks = kq % ksteps1, rr = a.reduce_reps > 0 ? kq / ksteps1 : rep;
       const int rb = t / col_blocks, cb = t % col_blocks;
       float* const sa = ring + st * C::kStageFloats;
       mbar_arrive_expect_tx(full + st, C::kStageBytes);
-      tma_load_3d(sa, &tm_lhs, ks * BK, rb * BM, rep, full + st);
-      tma_load_3d(sa + BM * BK, &tm_rhs, ks * BK, cb * BN, rep, full + st);
+      tma_load_3d(sa, &tm_lhs, ks * BK, rb * BM, rr, full + st);
+      tma_load_3d(sa + BM * BK, &tm_rhs, ks * BK, cb * BN, rr, full + st);
     }
     __syncwarp();
   };
@@ -439,7 +441,8 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
   const long long total = (long long)row_blocks * col_blocks;
   // One wave of 2 CTAs per SM when the replicas do not already fill the machine.
   const int slots = 2 * sm_count();
-  int per_cta = (int)((total * replicas + slots - 1) / slots);
+  const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;
+  int per_cta = (int)((total * grid_reps + slots - 1) / slots);
   per_cta = per_cta < 1 ? 1 : (per_cta > col_blocks ? col_blocks : per_cta);
   const int ctas = (int)((total + per_cta - 1) / per_cta);
   // Stream-ordered scratch for the bitmap view (12 bytes per (row, 64-column block)).
@@ -460,7 +463,7 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
     set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  dim3 grid(ctas, replicas);
+  dim3 grid(ctas, grid_reps);
   if (v1)
     sddmm_tiled_kernel<<<grid, C::THREADS, C::kSmemBytes, stream>>>(a, guard, per_cta, col_blocks,
                                                                     (int)total, masks, bases, tm_lhs, tm_rhs);

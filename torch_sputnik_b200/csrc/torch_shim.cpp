@@ -140,9 +140,9 @@ torch::Tensor spmm_bias_relu(int m, int k, torch::Tensor values, torch::Tensor r
                    false, "spmm_bias_relu");
 }
 
-// src/sputnik.cpp:18-23 -> src/sddmm_cuda.cu:7-57
-torch::Tensor sddmm(int m, int n, torch::Tensor row_indices_in, torch::Tensor row_offsets,
-                    torch::Tensor column_indices, torch::Tensor lhs, torch::Tensor rhs) {
+static torch::Tensor sddmm_impl(int m, int n, const torch::Tensor& row_indices_in,
+                                const torch::Tensor& row_offsets, const torch::Tensor& column_indices,
+                                const torch::Tensor& lhs, const torch::Tensor& rhs, bool reduce) {
   TORCH_CHECK(lhs.dim() == 2 || lhs.dim() == 3, "torch_sputnik.sddmm: lhs must be 2-D or 3-D");
   TORCH_CHECK(lhs.dim() == rhs.dim(), "torch_sputnik.sddmm: lhs and rhs must have the same rank");
   TSP_CHECK_CUDA_F32(lhs, "lhs_matrix");
@@ -162,14 +162,27 @@ torch::Tensor sddmm(int m, int n, torch::Tensor row_indices_in, torch::Tensor ro
               "torch_sputnik.sddmm: first dims of lhs and rhs must match");
 
   auto options = torch::TensorOptions().dtype(torch::kFloat32).device(lhs.device());
-  torch::Tensor out = replicas == 1 ? torch::empty({nnz}, options)
-                                    : torch::empty({replicas, nnz}, options);
-  check_rc(tsp_sddmm_f32(m, (int)k, n, (int)nnz, (int)replicas, row_indices.data_ptr<int>(),
-                         row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
-                         lhs.data_ptr<float>(), rhs.data_ptr<float>(), out.data_ptr<float>(),
-                         current_stream()),
-           "sddmm");
+  torch::Tensor out = (replicas == 1 || reduce) ? torch::empty({nnz}, options)
+                                                : torch::empty({replicas, nnz}, options);
+  auto fn = (reduce && replicas > 1) ? tsp_sddmm_reduce_f32 : tsp_sddmm_f32;
+  check_rc(fn(m, (int)k, n, (int)nnz, (int)replicas, row_indices.data_ptr<int>(),
+              row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(), lhs.data_ptr<float>(),
+              rhs.data_ptr<float>(), out.data_ptr<float>(), current_stream()),
+           reduce ? "sddmm_reduce" : "sddmm");
   return out;
+}
+
+// src/sputnik.cpp:18-23 -> src/sddmm_cuda.cu:7-57
+torch::Tensor sddmm(int m, int n, torch::Tensor row_indices, torch::Tensor row_offsets,
+                    torch::Tensor column_indices, torch::Tensor lhs, torch::Tensor rhs) {
+  return sddmm_impl(m, n, row_indices, row_offsets, column_indices, lhs, rhs, false);
+}
+
+// sddmm summed over the replica dimension -> [nnz]: what modules/sparse_linear.py:44 + autograd's
+// broadcast-sum compute for the weight gradient, without the [R, nnz] intermediate.
+torch::Tensor sddmm_reduce(int m, int n, torch::Tensor row_indices, torch::Tensor row_offsets,
+                           torch::Tensor column_indices, torch::Tensor lhs, torch::Tensor rhs) {
+  return sddmm_impl(m, n, row_indices, row_offsets, column_indices, lhs, rhs, true);
 }
 
 static torch::Tensor softmax_impl(const torch::Tensor& values, const torch::Tensor& row_indices_in,
@@ -316,6 +329,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("sparse_softmax_backward", &sparse_softmax_backward, "gradient of sparse_softmax_scaled");
   m.def("csr_transpose_with_perm", &csr_transpose_with_perm, "csr_transpose + permutation");
   m.def("permute_values", &permute_values, "values[..., perm]");
+  m.def("sddmm_reduce", &sddmm_reduce, "sum over replicas of sddmm -> [nnz] (sparse-linear weight gradient)");
   m.def("set_variant", [](const std::string& op, int v) { return tsp_set_variant(op.c_str(), v); },
         "force a kernel variant (benchmarking only)");
   m.def("launch_count", []() { return tsp_launch_count(); }, "kernels launched so far");

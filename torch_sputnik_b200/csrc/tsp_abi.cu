@@ -138,9 +138,23 @@ int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
 }
 
 // ----------------------------------------------------------------------------------- SDDMM
-int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_indices,
-                  const int* row_offsets, const int* column_indices, const float* lhs,
-                  const float* rhs, float* out, void* stream_) {
+static void launch_sddmm_gather_any(const SddmmArgs& a, int replicas, cudaStream_t stream) {
+  const int k = a.k;
+  const bool vec4_ok = (k % 4 == 0) && aligned16(a.lhs) && aligned16(a.rhs);
+  if (vec4_ok) {
+    if (k <= 32) launch_sddmm_gather<4, 8>(a, replicas, stream);
+    else if (k <= 64) launch_sddmm_gather<4, 16>(a, replicas, stream);
+    else launch_sddmm_gather<4, 32>(a, replicas, stream);
+  } else {
+    if (k <= 8) launch_sddmm_gather<1, 8>(a, replicas, stream);
+    else if (k <= 16) launch_sddmm_gather<1, 16>(a, replicas, stream);
+    else launch_sddmm_gather<1, 32>(a, replicas, stream);
+  }
+}
+
+static int sddmm_impl(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                      const int* row_offsets, const int* column_indices, const float* lhs,
+                      const float* rhs, float* out, void* stream_, bool reduce) {
   (void)row_indices;  // the flat-nonzero decomposition is balanced without a row swizzle
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
@@ -158,6 +172,45 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
   a.lhs = lhs;
   a.rhs = rhs;
   a.out = out;
+  if (reduce) {
+    // out[j] = sum over replicas: only the staged kernels fold the replica loop into their k loop;
+    // anything else computes [replicas, nnz] into stream-ordered scratch and sums it.
+    const double dens = (double)nnz / ((double)m * (double)n);
+    a.reduce_reps = replicas;
+    StagedGuard guard;
+    int rc = -1;
+    if (dens >= 0.22 && sddmm_tiled_applicable(a, replicas)) rc = launch_sddmm_tiled(a, replicas, stream, &guard, false);
+    else if (dens >= 0.015 && sddmm_sampled_applicable(a, replicas))
+      rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load(), g_sddmm_p.load());
+    if (rc > 0) return rc;
+    float* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&scratch), sizeof(float) * (size_t)replicas * nnz, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_reduce_f32 (scratch)");
+    int rc2;
+    if (rc == 0) {
+      // The staged kernel wrote out[] unless the columns turned out unsorted; in that case the
+      // guarded gather + reduce below (which exit at once otherwise) redo the work.
+      SddmmArgs f = a;
+      f.reduce_reps = 0;
+      f.out = scratch;
+      f.guard_slot = guard.slot;
+      f.guard_id = guard.call_id;
+      launch_sddmm_gather_any(f, replicas, stream);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      rc2 = cudaGetLastError() == cudaSuccess ? TSP_OK : TSP_ERR_CUDA;
+    } else {
+      rc2 = sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, scratch,
+                       stream_, false);
+    }
+    if (rc2 == TSP_OK) {
+      reduce_replicas_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(scratch, nnz, replicas, out,
+                                                                     rc == 0 ? guard.slot : 0, rc == 0 ? guard.call_id : 0u);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      if (cudaGetLastError() != cudaSuccess) rc2 = TSP_ERR_CUDA;
+    }
+    cudaFreeAsync(scratch, stream);
+    return rc2;
+  }
 
   // variant: 0 = heuristic, 1 = gather, 2 = tiled (dense register tiles, sampled), 3 = sampled
   // (TMA-staged operands, only the sampled products), 4 = tiled v1,
@@ -186,18 +239,21 @@ int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_ind
     a.guard_id = guard.call_id;
   }
 
-  const bool vec4_ok = (k % 4 == 0) && aligned16(lhs) && aligned16(rhs);
-  if (vec4_ok) {
-    if (k <= 32) launch_sddmm_gather<4, 8>(a, replicas, stream);
-    else if (k <= 64) launch_sddmm_gather<4, 16>(a, replicas, stream);
-    else launch_sddmm_gather<4, 32>(a, replicas, stream);
-  } else {
-    if (k <= 8) launch_sddmm_gather<1, 8>(a, replicas, stream);
-    else if (k <= 16) launch_sddmm_gather<1, 16>(a, replicas, stream);
-    else launch_sddmm_gather<1, 32>(a, replicas, stream);
-  }
+  launch_sddmm_gather_any(a, replicas, stream);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (gather)");
   return TSP_OK;
+}
+
+int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                  const int* row_offsets, const int* column_indices, const float* lhs,
+                  const float* rhs, float* out, void* stream) {
+  return sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, out, stream, false);
+}
+
+int tsp_sddmm_reduce_f32(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                         const int* row_offsets, const int* column_indices, const float* lhs,
+                         const float* rhs, float* out, void* stream) {
+  return sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, out, stream, true);
 }
 
 // --------------------------------------------------------------------------------- softmax

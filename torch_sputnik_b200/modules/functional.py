@@ -79,10 +79,12 @@ class Spmm(torch.autograd.Function):
         grad_values = grad_dense = None
         if ctx.needs_input_grad[2]:
             # dA = (dC @ B^T) sampled at the pattern; sddmm wants the right operand as [k, n].
-            grad_values = ops.sddmm(m, k, row_indices, row_offsets, column_indices, grad_output,
-                                    dense.contiguous())
-            if values.dim() == 1 and grad_values.dim() == 2:
-                grad_values = grad_values.sum(0)
+            if values.dim() == 1 and grad_output.dim() == 3:
+                grad_values = ops.sddmm_reduce(m, k, row_indices, row_offsets, column_indices, grad_output,
+                                               dense.contiguous())
+            else:
+                grad_values = ops.sddmm(m, k, row_indices, row_offsets, column_indices, grad_output,
+                                        dense.contiguous())
         if ctx.needs_input_grad[6]:
             t = TransposedTopology.get(m, k, row_offsets, column_indices)
             values_t = ops.permute_values(values.contiguous(), t.perm)
@@ -160,9 +162,9 @@ class SparseLinearFunction(torch.autograd.Function):
         grad_output = grad_output.contiguous()
         grad_values = grad_dense = None
         if ctx.needs_input_grad[2]:
-            gv = ops.sddmm(m, k, row_indices, row_offsets, column_indices, grad_output,
-                           dense.contiguous())
-            grad_values = gv.sum(0) if gv.dim() == 2 else gv
+            # one [nnz] vector straight from the kernel: the replica (batch) sum is folded into its k loop
+            grad_values = ops.sddmm_reduce(m, k, row_indices, row_offsets, column_indices, grad_output,
+                                           dense.contiguous())
         if ctx.needs_input_grad[6]:
             t = TransposedTopology.get(m, k, row_offsets, column_indices)
             values_t = ops.permute_values(values.contiguous(), t.perm)
