@@ -127,3 +127,35 @@ def test_sparse_attention_module_forward_backward_runs(dev):
     assert x.grad is not None and torch.isfinite(x.grad).all()
     for lin in att.linears:
         assert lin.values.grad is not None and torch.isfinite(lin.values.grad).all()
+
+
+def test_sparse_transformer_trains_and_buckets_gradients(dev):
+    """configs[4] model at toy size: a few SGD steps through SparseLinear / SparseAttention with the
+    gradients accumulated straight into the data-parallel buckets (world size 1 here)."""
+    from torch_sputnik_b200 import dist as tdist
+    from torch_sputnik_b200.modules.transformer import SparseTransformer
+    torch.manual_seed(0)
+    model = SparseTransformer(layers=2, hidden=64, heads=2, ffn=128, seq_len=64, vocab=50,
+                              linear_sparsity=0.7, attn_sparsity=0.7, device=dev).to(dev)
+    model.setup_sparse()
+    sparse = tdist.sparse_value_parameters(model)
+    assert len(sparse) == 2 * (4 + 2)
+    ids = {id(p) for p in sparse}
+    dense = [p for p in model.parameters() if p.requires_grad and id(p) not in ids]
+    b_sparse, b_dense = tdist.ValueGradBucket(sparse), tdist.ValueGradBucket(dense)
+    tokens = torch.randint(0, 50, (2, 64), device=dev)
+    target = torch.randint(0, 50, (2, 64), device=dev)
+    losses = []
+    for _ in range(8):
+        b_sparse.zero_()
+        b_dense.zero_()
+        loss = torch.nn.functional.cross_entropy(model(tokens).reshape(-1, 50), target.reshape(-1))
+        loss.backward()
+        b_sparse.all_reduce().wait()
+        assert sparse[0].grad.data_ptr() == b_sparse.flat.data_ptr()     # still a view of the bucket
+        assert torch.isfinite(b_sparse.flat).all() and float(b_sparse.flat.abs().sum()) > 0
+        with torch.no_grad():
+            for p in sparse + dense:
+                p.add_(p.grad, alpha=-0.05)
+        losses.append(float(loss))
+    assert all(np.isfinite(losses)) and losses[-1] < losses[0]

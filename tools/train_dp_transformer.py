@@ -1,0 +1,119 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[4]: data-parallel training step of the sparse Transformer
+(torch_sputnik_b200/modules/transformer.py) -- 90 %-sparse linear layers, shared-mask sparse
+attention -- with ONE NCCL all-reduce of the nnz-long value gradients per step (plus one for the
+small dense parameters).  One process per GPU:
+
+    python tools/train_dp_transformer.py [--steps 10] [--batch 4]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \\
+        --master-port 29500 tools/train_dp_transformer.py
+
+Prints one JSON line on rank 0: tokens/s over all ranks (weak scaling: --batch sequences per GPU),
+ms per step (max over ranks, CUDA events), bytes all-reduced per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch_sputnik_b200  # noqa: E402,F401
+import torch_sputnik as ops  # noqa: E402
+from torch_sputnik_b200 import dist as tdist  # noqa: E402
+from torch_sputnik_b200.modules.transformer import SparseTransformer  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=4)
+    ap.add_argument("--layers", type=int, default=6)
+    ap.add_argument("--hidden", type=int, default=512)
+    ap.add_argument("--heads", type=int, default=8)
+    ap.add_argument("--ffn", type=int, default=2048)
+    ap.add_argument("--seq", type=int, default=512)
+    ap.add_argument("--lr", type=float, default=1e-2)
+    args = ap.parse_args()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.distributed.init_process_group("nccl", device_id=dev)
+
+    torch.manual_seed(0)                       # identical initial weights and masks on every rank
+    vocab = 1000
+    model = SparseTransformer(args.layers, args.hidden, args.heads, args.ffn, args.seq, vocab, device=dev).to(dev)
+    model.setup_sparse()
+    sparse = tdist.sparse_value_parameters(model)
+    sparse_ids = {id(p) for p in sparse}
+    dense = [p for p in model.parameters() if p.requires_grad and id(p) not in sparse_ids]
+    tdist.broadcast_parameters(sparse + dense)
+    b_sparse = tdist.ValueGradBucket(sparse)
+    b_dense = tdist.ValueGradBucket(dense)
+
+    g = torch.Generator(device="cpu").manual_seed(100 + rank)   # each rank its own token shard
+    tokens = torch.randint(0, vocab, (args.batch, args.seq), generator=g).to(dev)
+    target = torch.randint(0, vocab, (args.batch, args.seq), generator=g).to(dev)
+    loss_fn = torch.nn.CrossEntropyLoss()
+
+    def step():
+        b_sparse.zero_()
+        b_dense.zero_()
+        logits = model(tokens)
+        loss = loss_fn(logits.reshape(-1, vocab), target.reshape(-1))
+        loss.backward()
+        b_sparse.all_reduce()                  # side stream: overlaps the dense bucket's launch
+        b_dense.all_reduce()
+        b_sparse.wait()
+        b_dense.wait()
+        with torch.no_grad():
+            for p in sparse + dense:
+                p.add_(p.grad, alpha=-args.lr)
+        return loss
+
+    losses = []
+    for _ in range(args.warmup):
+        losses.append(float(step()))
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    l0 = ops.launch_count()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(args.steps):
+        loss = step()
+    e.record()
+    torch.cuda.synchronize()
+    losses.append(float(loss))
+    ms = torch.tensor([s.elapsed_time(e) / args.steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+    if rank == 0:
+        ms = float(ms)
+        print(json.dumps({
+            "config": "C5: data-parallel sparse Transformer, 90% sparse linear layers + shared-mask sparse attention",
+            "n_gpus": world, "ms_per_step": round(ms, 3),
+            "tokens_per_s": round(world * args.batch * args.seq / (ms * 1e-3), 1), "scaling": "weak",
+            "model": {"layers": args.layers, "hidden": args.hidden, "heads": args.heads, "ffn": args.ffn,
+                      "seq": args.seq, "batch_per_gpu": args.batch},
+            "allreduce_bytes_per_step": {"sparse_values": b_sparse.nbytes, "dense_params": b_dense.nbytes,
+                                         "dense_equivalent_of_sparse": 10 * b_sparse.nbytes},
+            "tsp_kernel_launches_per_step": (ops.launch_count() - l0) // args.steps,
+            "loss_first_last": [round(losses[0], 4), round(losses[-1], 4)]}), flush=True)
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
