@@ -37,6 +37,16 @@ METRIC = "SpMM+SDDMM useful GFLOP/s, 4096^3, density 0.05-0.5 (fp32 CSR)"
 UNIT = "GFLOP/s"
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel behind (op, density), from the
+# `ncu --set full` captures summarised under profiles/ (r01_*_ncu_summary.txt); None = not captured.
+NCU_DRAM_TRAFFIC = {
+    ("spmm", 0.5): 560.6e6,     # profiles/r01_spmm_staged_d050_ncu_summary.txt
+    ("sddmm", 0.5): 1260.6e6,   # profiles/r01_sddmm_tiled2_d050_ncu_summary.txt
+    ("spmm", 0.05): 112.8e6,    # profiles/r01_spmm_gather_d005_ncu_summary.txt
+    ("sddmm", 0.05): 211.5e6,   # profiles/r01_sddmm_sampled_v2_d005_ncu_summary.txt
+}
+
+
 def spmm_bytes(m, k, n, nnz):   # every operand once
     return 8 * nnz + 4 * (2 * m + 1) + 4 * k * n + 4 * m * n
 
@@ -201,6 +211,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     import torch_sputnik_b200  # noqa: F401  (registers torch_sputnik; raises if not built)
@@ -331,7 +343,9 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": f"{top['op']} d={top['density']}",
                          "achieved": top["algorithmic_gbs"], "peak": peak, "peak_kind": peak_kind,
-                         "unit": "GB/s", "frac": top["hbm_frac"], "traffic": None,
+                         "unit": "GB/s", "frac": top["hbm_frac"],
+                         "traffic": NCU_DRAM_TRAFFIC.get((top["op"], top["density"])),
+                         "algorithmic_bytes": top["algorithmic_bytes"],
                          "fp32_frac": top["fp32_frac"], "avg_launch_ms": top["ms"],
                          "note": "unstructured CSR at these shapes is bound by shared-memory/L1 gather "
                                  "bandwidth and fp32 issue, not HBM (DESIGN.md); fp32_frac is vs "

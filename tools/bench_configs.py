@@ -190,6 +190,8 @@ def main():
     dev = torch.device("cuda", LOCAL)
     if WORLD > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         torch.distributed.init_process_group("nccl", device_id=dev)
     flush = torch.zeros(64 * 1024 * 1024, device=dev)   # 256 MB > L2
     if args.config in ("c1", "all"):

@@ -48,6 +48,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         torch.distributed.init_process_group("nccl", device_id=dev)
 
     torch.manual_seed(0)                       # identical initial weights and masks on every rank
