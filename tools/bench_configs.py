@@ -42,23 +42,29 @@ RANK = int(os.environ.get("RANK", "0"))
 LOCAL = int(os.environ.get("LOCAL_RANK", "0"))
 
 
+def _loop_ms(body, reps):
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    s.record()
+    for _ in range(reps):
+        body()
+    e.record()
+    e.synchronize()
+    return s.elapsed_time(e) / reps
+
+
 def timeit(fn, reps=20, warm=5, flush=None):
-    """Mean CUDA-event time of fn() in ms; `flush` (a big tensor) is rewritten between calls when the
-    working set is smaller than L2."""
+    """Mean device time of fn() in ms over `reps` back-to-back launches (CUDA events on the launching
+    stream, no host sync inside the loop, so host launch latency is pipelined as in real use).
+    `flush` (a tensor larger than L2) is rewritten between calls when the working set is smaller
+    than L2; its own time, measured the same way, is subtracted."""
     for _ in range(warm):
         fn()
-    torch.cuda.synchronize()
-    total = 0.0
-    for _ in range(reps):
-        if flush is not None:
-            flush.add_(1.0)
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        fn()
-        e.record()
-        e.synchronize()
-        total += s.elapsed_time(e)
-    ms = total / reps
+    if flush is None:
+        ms = _loop_ms(fn, reps)
+    else:
+        both = _loop_ms(lambda: (flush.add_(1.0), fn()), reps)
+        ms = both - _loop_ms(lambda: flush.add_(1.0), reps)
     if WORLD > 1:
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
@@ -190,8 +196,7 @@ def main():
     dev = torch.device("cuda", LOCAL)
     if WORLD > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version banner must not land on stdout
         torch.distributed.init_process_group("nccl", device_id=dev)
     flush = torch.zeros(64 * 1024 * 1024, device=dev)   # 256 MB > L2
     if args.config in ("c1", "all"):
