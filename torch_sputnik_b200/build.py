@@ -64,7 +64,7 @@ def build_libtsp(force: bool = False, verbose: bool = False) -> str:
 
 def build_shim(force: bool = False) -> str:
     src = os.path.join(CSRC, "torch_shim.cpp")
-    if not force and _newer(SHIM, [src, os.path.join(ROOT, "include", "tsp.h")]):
+    if not force and _newer(SHIM, [src, os.path.join(CSRC, "many_mask.inc"), os.path.join(ROOT, "include", "tsp.h")]):
         return SHIM
     import torch
     from torch.utils import cpp_extension as ce

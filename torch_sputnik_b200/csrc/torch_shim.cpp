@@ -13,6 +13,7 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/extension.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "../../include/tsp.h"
@@ -315,6 +316,8 @@ torch::Tensor permute_values(torch::Tensor values, torch::Tensor perm) {
   return out;
 }
 
+#include "many_mask.inc"
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.doc() = "B200-native CSR sparse kernels behind the torch_sputnik operator API";
   m.def("spmm", &spmm, "Sparse Matrix Matrix Multiplication: AxB");
@@ -330,6 +333,10 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("csr_transpose_with_perm", &csr_transpose_with_perm, "csr_transpose + permutation");
   m.def("permute_values", &permute_values, "values[..., perm]");
   m.def("sddmm_reduce", &sddmm_reduce, "sum over replicas of sddmm -> [nnz] (sparse-linear weight gradient)");
+  m.def("spmm_many_mask", &spmm_many_mask, "spmm with one CSR mask per batch element");
+  m.def("sddmm_many_mask", &sddmm_many_mask, "sddmm with one CSR mask per batch element");
+  m.def("sparse_softmax_many_mask", &sparse_softmax_many_mask, "sparse_softmax with one CSR mask per batch element");
+  m.def("csr_transpose_many_mask", &csr_transpose_many_mask, "csr_transpose with one CSR mask per batch element");
   m.def("set_variant", [](const std::string& op, int v) { return tsp_set_variant(op.c_str(), v); },
         "force a kernel variant (benchmarking only)");
   m.def("launch_count", []() { return tsp_launch_count(); }, "kernels launched so far");
