@@ -111,6 +111,22 @@ int tsp_csr_softmax_backward_f32(int m, int nnz, int replicas, float scale,
                                  float* dx, void* stream);
 
 /*
+ * Fused sparse attention forward (extension): the chain
+ * sddmm -> sparse_softmax(scale) -> spmm of modules/sparse_attention.py:66-82 in one kernel,
+ *   out[r, i, :] = sum_j softmax_j(scale * <q[r, i, :], k[r, col_j, :]>) * v[r, col_j, :]
+ * over the nonzeros j of mask row i.  q [replicas, m, d], k and v [replicas, n, d],
+ * out [replicas, m, d]; lse_or_null, if non-NULL, receives [replicas, m] log-sum-exp of the scaled
+ * scores (what a backward pass needs to rebuild the probabilities).  Rows without nonzeros give
+ * zeros (lse = -inf).  tsp_sparse_attention_supported(n, d) != 0 iff the head dimension is handled
+ * (d = 32, 64, 96, 128 and n * d < 2^29); operands must be 16-byte aligned.
+ */
+int tsp_sparse_attention_supported(int n, int d);
+int tsp_sparse_attention_f32(int m, int n, int d, int nnz, int replicas, float scale,
+                             const int* row_indices, const int* row_offsets,
+                             const int* column_indices, const float* q, const float* k,
+                             const float* v, float* out, float* lse_or_null, void* stream);
+
+/*
  * CSR transpose (m x n  ->  n x m), stable in the original nonzero order, which is what
  * cusparseCsr2cscEx2(CUSPARSE_CSR2CSC_ALG1) returns: inside each output row the entries
  * appear in ascending original row.  values is [replicas, nnz] (replicas >= 1; the

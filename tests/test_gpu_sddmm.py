@@ -224,14 +224,15 @@ def test_sddmm_through_raw_c_abi(dev):
 @pytest.mark.parametrize("m,n,k,density,reps", [
     (300, 1024, 64, 0.1, 1), (4096, 4096, 64, 0.1, 2), (130, 700, 32, 0.3, 3), (257, 520, 128, 0.2, 1),
     (129, 2048, 96, 0.06, 2), (64, 512, 64, 1.0, 1), (1000, 1000, 64, 0.15, 1)])
-def test_sddmm_rows_short_inner_dimension(ops, dev, m, n, k, density, reps):
+@pytest.mark.parametrize("variant", [5])
+def test_sddmm_rows_short_inner_dimension(ops, dev, m, n, k, density, reps, variant):
     """Forced rows variant (the attention Q @ K^T shape): ragged m / n, every k in {32..128},
     replicas, dense masks (rows longer than one 32-nonzero batch per band)."""
     a = random_csr(m, n, density, seed=m + n + k, values="pm1")
     lead = (reps,) if reps > 1 else ()
     lhs, rhs = dense_operand(lead + (m, k), 51, "pm1"), dense_operand(lead + (n, k), 52, "pm1")
     _, ri, ro, ci = to_dev(a, dev)
-    prev = ops.set_variant("sddmm", 5)
+    prev = ops.set_variant("sddmm", variant)
     try:
         got = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev)).cpu().numpy()
     finally:
@@ -244,7 +245,8 @@ def test_sddmm_rows_short_inner_dimension(ops, dev, m, n, k, density, reps):
         assert_close_fwd(g, f, scale, what=f"rows {m}x{n}x{k} replica {r}")
 
 
-def test_sddmm_rows_empty_rows_and_unsorted(ops, dev):
+@pytest.mark.parametrize("variant", [5])
+def test_sddmm_rows_empty_rows_and_unsorted(ops, dev, variant):
     m, n, k = 200, 1536, 64
     rng = np.random.default_rng(7)
     mask = rng.random((m, n)) < 0.15
@@ -256,7 +258,7 @@ def test_sddmm_rows_empty_rows_and_unsorted(ops, dev):
     for i in range(0, m, 3):                      # shuffled columns in every third row: still exact
         s_, e_ = a.row_offsets[i], a.row_offsets[i + 1]
         a.column_indices[s_:e_] = a.column_indices[s_:e_][rng.permutation(e_ - s_)]
-    prev = ops.set_variant("sddmm", 5)
+    prev = ops.set_variant("sddmm", variant)
     try:
         check_sddmm(ops, dev, a, dense_operand((m, k), 53, "pm1"), dense_operand((n, k), 54, "pm1"), "rows skew")
     finally:

@@ -184,6 +184,13 @@ def c4(dev, flush, replicas):
     total = ms_sddmm + ms_soft + ms_spmm
     emit("C4", "attention fwd (3 ops)", total, r * (16 * nnz + 16 * s * d) + 2 * topo + 4 * (2 * s + 1),
          4.0 * nnz * d * r, {"replicas_per_gpu": r, "replicas_total": replicas})
+    for w in [int(x) for x in os.environ.get("TSP_ATTN_WARPS", "0").split(",")]:
+        ops.set_variant("attn_warps", w)
+        ms_fused = timeit(lambda: ops.sparse_attention(s, s, ri, ro, ci, q, kk, vv, 0.125))
+        emit("C4", "attention fwd fused (1 kernel)" + (f" warps={w}" if w else ""), ms_fused,
+             r * 16 * s * d + topo + 4 * r * s, 4.0 * nnz * d * r,
+             {"replicas_per_gpu": r, "replicas_total": replicas, "three_op_chain_ms": round(total, 4)})
+    ops.set_variant("attn_warps", 0)
 
 
 def main():

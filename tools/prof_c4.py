@@ -1,5 +1,5 @@
 """One op at the attention shape (s=4096, d=64, 90 % sparse mask), few replicas -- for ncu captures.
-usage: python tools/prof_c4.py spmm|sddmm [REPLICAS] [REPS]   (TSP_VARIANT forces a kernel variant)"""
+usage: python tools/prof_c4.py spmm|sddmm|attn [REPLICAS] [REPS]   (TSP_VARIANT forces a kernel variant)"""
 import os
 import sys
 
@@ -15,9 +15,9 @@ from oracle.csr import random_csr  # noqa: E402
 op = sys.argv[1]
 R = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-if os.environ.get("TSP_VARIANT"):
+if os.environ.get("TSP_VARIANT") and op != "attn":
     ops.set_variant(op, int(os.environ["TSP_VARIANT"]))
-for knob in ("spmm_warps", "sddmm_warps"):
+for knob in ("spmm_warps", "sddmm_warps", "attn_warps"):
     if os.environ.get("TSP_" + knob.upper()):
         ops.set_variant(knob, int(os.environ["TSP_" + knob.upper()]))
 dev = torch.device("cuda:0")
@@ -32,6 +32,8 @@ ev[0].record()
 for i in range(reps):
     if op == "spmm":
         ops.spmm(s, s, p, ri, ro, ci, v)
+    elif op == "attn":
+        ops.sparse_attention(s, s, ri, ro, ci, q, k, v, 0.125)
     else:
         ops.sddmm(s, s, ri, ro, ci, q, k)
     ev[i + 1].record()

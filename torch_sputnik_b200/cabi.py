@@ -12,7 +12,8 @@ LIB_PATH = os.path.join(_HERE, "lib", "libtsp.so")
 SYMBOLS = (
     "tsp_version", "tsp_last_error", "tsp_spmm_f32", "tsp_sddmm_f32", "tsp_sddmm_reduce_f32", "tsp_csr_softmax_f32",
     "tsp_csr_softmax_backward_f32", "tsp_csr_transpose_workspace", "tsp_csr_transpose_f32",
-    "tsp_permute_values_f32", "tsp_set_variant", "tsp_launch_count",
+    "tsp_permute_values_f32", "tsp_sparse_attention_supported", "tsp_sparse_attention_f32", "tsp_set_variant",
+    "tsp_launch_count",
 )
 
 _lib = None
@@ -36,6 +37,8 @@ def load() -> ctypes.CDLL:
         lib.tsp_csr_transpose_workspace.restype = sz
         lib.tsp_csr_transpose_f32.argtypes = [i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
         lib.tsp_permute_values_f32.argtypes = [i, i, vp, vp, vp, vp]
+        lib.tsp_sparse_attention_supported.argtypes = [i, i]
+        lib.tsp_sparse_attention_f32.argtypes = [i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_set_variant.argtypes = [ctypes.c_char_p, i]
         lib.tsp_launch_count.restype = ctypes.c_ulonglong
         _lib = lib

@@ -14,6 +14,7 @@
 #include <torch/extension.h>
 
 #include <algorithm>
+#include <cstdint>
 #include <vector>
 
 #include "../../include/tsp.h"
@@ -316,6 +317,45 @@ torch::Tensor permute_values(torch::Tensor values, torch::Tensor perm) {
   return out;
 }
 
+// Extension: modules/sparse_attention.py:66-82 in one kernel.  q [R, m, d],
+// k and v [R, n, d] (or 2-D for R = 1) -> [out [R, m, d], lse [R, m]].  Head dimensions the fused
+// kernel does not take go through the three-op chain (lse is then left empty).
+std::vector<torch::Tensor> sparse_attention(int m, int n, torch::Tensor row_indices_in, torch::Tensor row_offsets,
+                                            torch::Tensor column_indices, torch::Tensor q, torch::Tensor k,
+                                            torch::Tensor v, double scale) {
+  TSP_CHECK_CUDA_F32(q, "q");
+  TSP_CHECK_CUDA_F32(k, "k");
+  TSP_CHECK_CUDA_F32(v, "v");
+  TORCH_CHECK(q.dim() == k.dim() && q.dim() == v.dim() && (q.dim() == 2 || q.dim() == 3),
+              "torch_sputnik.sparse_attention: q, k, v must all be 2-D or all 3-D");
+  c10::cuda::CUDAGuard guard(q.device());
+  torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
+  check_topology(m, row_indices, row_offsets, column_indices);
+  const int off = q.dim() - 2;
+  const int64_t replicas = off ? q.size(0) : 1, d = q.size(off + 1);
+  TORCH_CHECK(q.size(off) == m && k.size(off) == n && v.size(off) == n && k.size(off + 1) == d &&
+                  v.size(off + 1) == d && (!off || (k.size(0) == replicas && v.size(0) == replicas)),
+              "torch_sputnik.sparse_attention: expected q [R, m, d], k [R, n, d], v [R, n, d]");
+  const int64_t nnz = column_indices.size(0);
+  const bool aligned = ((reinterpret_cast<uintptr_t>(q.data_ptr()) | reinterpret_cast<uintptr_t>(k.data_ptr()) |
+                         reinterpret_cast<uintptr_t>(v.data_ptr())) & 15) == 0;
+  if (!aligned || !tsp_sparse_attention_supported(n, (int)d)) {
+    torch::Tensor scores = sddmm_impl(m, n, row_indices, row_offsets, column_indices, q, k, false);
+    torch::Tensor probs = softmax_impl(scores, row_indices, row_offsets, column_indices, scale);
+    torch::Tensor out = spmm_impl(m, n, probs, row_indices, row_offsets, column_indices, v, c10::nullopt, false,
+                                  false, "sparse_attention");
+    return {out.reshape(q.sizes()), torch::empty({0}, q.options())};
+  }
+  torch::Tensor out = torch::empty_like(q);
+  torch::Tensor lse = torch::empty(off ? std::vector<int64_t>{replicas, m} : std::vector<int64_t>{m}, q.options());
+  check_rc(tsp_sparse_attention_f32(m, n, (int)d, (int)nnz, (int)replicas, (float)scale, row_indices.data_ptr<int>(),
+                                    row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                                    q.data_ptr<float>(), k.data_ptr<float>(), v.data_ptr<float>(),
+                                    out.data_ptr<float>(), lse.data_ptr<float>(), current_stream()),
+           "sparse_attention");
+  return {out, lse};
+}
+
 #include "many_mask.inc"
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
@@ -333,6 +373,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("csr_transpose_with_perm", &csr_transpose_with_perm, "csr_transpose + permutation");
   m.def("permute_values", &permute_values, "values[..., perm]");
   m.def("sddmm_reduce", &sddmm_reduce, "sum over replicas of sddmm -> [nnz] (sparse-linear weight gradient)");
+  m.def("sparse_attention", &sparse_attention, "fused sddmm -> softmax(scale) -> spmm; returns [out, lse]");
   m.def("spmm_many_mask", &spmm_many_mask, "spmm with one CSR mask per batch element");
   m.def("sddmm_many_mask", &sddmm_many_mask, "sddmm with one CSR mask per batch element");
   m.def("sparse_softmax_many_mask", &sparse_softmax_many_mask, "sparse_softmax with one CSR mask per batch element");

@@ -16,6 +16,7 @@
 #include "kernels/sddmm_staged.cuh"
 #include "kernels/sddmm_sampled.cuh"
 #include "kernels/sddmm_rows.cuh"
+#include "kernels/attention_rows.cuh"
 
 namespace tsp {
 
@@ -24,6 +25,7 @@ std::atomic<unsigned long long> g_launches{0};
 static std::atomic<int> g_spmm_variant{0};
 std::atomic<int> g_spmm_warps{0};
 std::atomic<int> g_sddmm_warps{0};
+std::atomic<int> g_attn_warps{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_sddmm_bn{0};
 static std::atomic<int> g_sddmm_p{0};
@@ -72,6 +74,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm") == 0) return g_spmm_variant.exchange(variant);
   if (op && strcmp(op, "spmm_warps") == 0) return g_spmm_warps.exchange(variant);
   if (op && strcmp(op, "sddmm_warps") == 0) return g_sddmm_warps.exchange(variant);
+  if (op && strcmp(op, "attn_warps") == 0) return g_attn_warps.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
@@ -290,6 +293,36 @@ int tsp_csr_softmax_f32(int m, int nnz, int replicas, float scale, const float* 
     default: csr_softmax_kernel<32, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
   }
   TSP_CHECK_LAUNCH("tsp_csr_softmax_f32");
+  return TSP_OK;
+}
+
+int tsp_sparse_attention_supported(int n, int d) {
+  return d >= 32 && d <= 128 && d % 32 == 0 &&
+         (unsigned long long)n * (unsigned long long)d * 4ull < (1ull << 31);
+}
+
+int tsp_sparse_attention_f32(int m, int n, int d, int nnz, int replicas, float scale,
+                             const int* row_indices, const int* row_offsets,
+                             const int* column_indices, const float* q, const float* k,
+                             const float* v, float* out, float* lse_or_null, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  (void)row_indices;   // rows are taken in order: neighbouring rows share k / v rows in L1
+  if (m < 0 || n < 0 || d < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_sparse_attention_f32: negative dimension");
+  if (replicas > 65535) return invalid("tsp_sparse_attention_f32: replicas=%d exceeds 65535", replicas);
+  if (m == 0 || replicas == 0) return TSP_OK;
+  if (!tsp_sparse_attention_supported(n, d))
+    return invalid("tsp_sparse_attention_f32: head dimension %d (n=%d) not supported; use the three-op chain", d, n);
+  if (!row_offsets || !q || !k || !v || !out || (nnz > 0 && !column_indices))
+    return invalid("tsp_sparse_attention_f32: null pointer argument");
+  AttnArgs a;
+  a.m = m; a.n = n; a.d = d; a.nnz = nnz;
+  a.row_offsets = row_offsets; a.column_indices = column_indices;
+  a.q = q; a.k = k; a.v = v; a.out = out; a.lse = lse_or_null; a.scale = scale;
+  if (!attention_rows_applicable(a))
+    return invalid("tsp_sparse_attention_f32: q, k, v and out must be 16-byte aligned");
+  launch_attention_rows(a, replicas, stream);
+  TSP_CHECK_LAUNCH("tsp_sparse_attention_f32");
   return TSP_OK;
 }
 
