@@ -46,6 +46,24 @@ NCU_DRAM_TRAFFIC = {
     ("sddmm", 0.05): 211.5e6,   # profiles/r01_sddmm_sampled_v2_d005_ncu_summary.txt
 }
 
+_RESULT_OUT = None
+
+
+def protect_stdout():
+    """Route fd 1 to stderr for the rest of the process and keep the real stdout for the result
+    line only: NCCL writes its version banner to fd 1 from C, which would precede the JSON line."""
+    global _RESULT_OUT
+    if _RESULT_OUT is None:
+        sys.stdout.flush()
+        _RESULT_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit_line(text):
+    out = _RESULT_OUT or sys.stdout
+    out.write(text + "\n")
+    out.flush()
+
 
 def spmm_bytes(m, k, n, nnz):   # SURVEY.md 8(d): every operand once
     return 8 * nnz + 4 * (2 * m + 1) + 4 * k * n + 4 * m * n
@@ -193,7 +211,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_line(json.dumps(line))
     return 0
 
 
@@ -222,6 +240,9 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from torch_sputnik_b200.host import HostPipeline, bind_to_gpu_numa_node
+    numa_cores = bind_to_gpu_numa_node(local) if world > 1 else []   # before the pinned allocations below
+
     cases = make_workload(rank, DIM, DENSITIES)
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a))
     for c in cases:
@@ -248,7 +269,6 @@ def run_ours(args):
             if events is not None:
                 events[2 * i + 1][1].record()
 
-    from torch_sputnik_b200.host import HostPipeline
     pipe = HostPipeline(dev)
 
     def e2e_step():
@@ -367,7 +387,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps,
                     "api": "torch_sputnik_b200.host.HostPipeline (pinned host operands; upload / kernel / "
                            "download streams overlapped across calls)",
-                    "serial_ms_per_step": e2e_serial_ms,
+                    "serial_ms_per_step": e2e_serial_ms, "numa_bound_cores": len(numa_cores),
                     "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1)},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": f"{top['op']} d={top['density']}",
@@ -387,7 +407,7 @@ def run_ours(args):
             ref = reference_kernel_leg(cases, dev, torch)
             if ref is not None:
                 line["reference_kernel_same_box"] = ref
-        print(json.dumps(line), flush=True)
+        emit_line(json.dumps(line))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -452,6 +472,7 @@ def reference_kernel_leg(cases, dev, torch):
 
 
 def main():
+    protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

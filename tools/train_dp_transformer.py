@@ -29,6 +29,9 @@ from torch_sputnik_b200.modules.transformer import SparseTransformer  # noqa: E4
 
 
 def main():
+    real_out = os.fdopen(os.dup(1), "w")   # fd 1 -> stderr from here on: NCCL prints its banner to fd 1
+    sys.stdout.flush()
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
@@ -101,7 +104,7 @@ def main():
         torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
     if rank == 0:
         ms = float(ms)
-        print(json.dumps({
+        real_out.write(json.dumps({
             "config": "C5: data-parallel sparse Transformer, 90% sparse linear layers + shared-mask sparse attention",
             "n_gpus": world, "ms_per_step": round(ms, 3),
             "tokens_per_s": round(world * args.batch * args.seq / (ms * 1e-3), 1), "scaling": "weak",
@@ -110,7 +113,8 @@ def main():
             "allreduce_bytes_per_step": {"sparse_values": b_sparse.nbytes, "dense_params": b_dense.nbytes,
                                          "dense_equivalent_of_sparse": 10 * b_sparse.nbytes},
             "tsp_kernel_launches_per_step": (ops.launch_count() - l0) // args.steps,
-            "loss_first_last": [round(losses[0], 4), round(losses[-1], 4)]}), flush=True)
+            "loss_first_last": [round(losses[0], 4), round(losses[-1], 4)]}) + "\n")
+        real_out.flush()
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()

@@ -24,6 +24,29 @@ import torch
 from . import torch_sputnik as _ops
 
 
+def bind_to_gpu_numa_node(index: int) -> list[int]:
+    """Pin this process to the CPU cores NVML reports as local to GPU `index`, so that the pinned
+    host buffers allocated afterwards (first touch) and the copy submission threads live on the
+    NUMA node the GPU's PCIe root hangs off.  With one process per GPU on a two-socket box this is
+    what keeps eight concurrent uploads from funnelling through one socket.  Best effort: returns
+    the cores bound to, or [] when NVML / sched_setaffinity are unavailable."""
+    try:
+        import os
+
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cores = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        allowed = sorted(set(cores) & os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return []
+
+
 class Staged:
     """Device copies of a group of host tensors + the event that marks their arrival."""
     __slots__ = ("tensors", "ready", "nbytes")
