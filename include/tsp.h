@@ -69,6 +69,19 @@ int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
                  const float* bias_or_null, int relu, float* out, void* stream);
 
 /*
+ * SpMM through a value permutation (extension): as tsp_spmm_f32, but nonzero p of the CSR arrays
+ * takes its value from values[r, value_perm[p]].  With (row_offsets, column_indices, perm) the
+ * output of tsp_csr_transpose_f32 for a static topology, this multiplies by A_r^T without first
+ * writing the permuted [replicas, nnz] values (the backward passes of modules/spmm.py:59-67 and
+ * modules/sddmm.py:60-68 do a csr_transpose per call).  value_perm_or_null == NULL: identical to
+ * tsp_spmm_f32.
+ */
+int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
+                      const int* row_indices, const float* values, const int* value_perm_or_null,
+                      const int* row_offsets, const int* column_indices, const float* dense,
+                      const float* bias_or_null, int relu, float* out, void* stream);
+
+/*
  * SDDMM: out[r, j] = dot(lhs[r, row_of(j), :], rhs[r, column_indices[j], :])
  *   lhs is [replicas, m, k], rhs is [replicas, n, k] (i.e. the right operand already
  *   transposed, as in the reference), out is [replicas, nnz].  Exactly nnz values per

@@ -260,3 +260,36 @@ def test_spmm_narrow_operand_wide_ctas(ops, dev, m, k, n, density, reps, warps):
         ref = oracle.spmm(m, k, vr, a.row_offsets, a.column_indices, br)
         scale = oracle.spmm_abs(m, k, vr, a.row_offsets, a.column_indices, br)
         assert_close_fwd(got[r] if reps > 1 else got, ref, scale, what=f"narrow {m}x{k}x{n} replica {r}")
+
+
+@pytest.mark.parametrize("m,k,n,density,reps,variant", [
+    (300, 260, 64, 0.1, 3, 0),       # attention backward shape class: gather kernel, 2-D values
+    (256, 512, 256, 0.5, 2, 2),      # staged kernel reads its candidates through the permutation too
+    (130, 90, 33, 0.3, 1, 0),        # scalar path, 1-D values
+])
+def test_spmm_perm_multiplies_by_the_transpose(ops, dev, m, k, n, density, reps, variant):
+    """spmm_perm(transposed topology, ORIGINAL values, perm) == A^T @ dense: bit-identical to
+    spmm on explicitly permuted values, and within the bound of the oracle on the transpose."""
+    a = random_csr(m, k, density, seed=5 * m + n, values="pm1")
+    lead = (reps,) if reps > 1 else ()
+    vals = dense_operand(lead + (a.nnz,), 61, "pm1")
+    dense = dense_operand(lead + (m, n), 62, "pm1")
+    _, _, ro, ci = to_dev(a, dev)
+    tv, td = torch.from_numpy(vals).to(dev), torch.from_numpy(dense).to(dev)
+    probe = torch.empty(a.nnz, device=dev)
+    _, rot, cit, perm = ops.csr_transpose_with_perm(m, k, probe, ro, ci)
+    rit = torch.argsort(rot[1:] - rot[:-1], descending=True, stable=True).to(torch.int32)
+    prev = ops.set_variant("spmm", variant)
+    try:
+        got = ops.spmm_perm(k, m, tv, perm, rit, rot, cit, td)
+        explicit = ops.spmm(k, m, ops.permute_values(tv, perm), rit, rot, cit, td)
+    finally:
+        ops.set_variant("spmm", prev)
+    assert torch.equal(got, explicit)
+    got = got.cpu().numpy().reshape(lead + (k, n))
+    for r in range(reps):
+        v_r, d_r = (vals[r], dense[r]) if reps > 1 else (vals, dense)
+        vt, rot_o, cit_o, _ = oracle.csr_transpose(m, k, v_r, a.row_offsets, a.column_indices)
+        ref = oracle.spmm(k, m, vt, rot_o, cit_o, d_r)
+        scale = oracle.spmm_abs(k, m, vt, rot_o, cit_o, d_r)
+        assert_close_fwd(got[r] if reps > 1 else got, ref, scale, what=f"spmm_perm replica {r}")

@@ -215,6 +215,12 @@ def c4(dev, flush, replicas):
     _, rot, cit, perm = ops.csr_transpose_with_perm(s, s, probs[0].contiguous(), ro, ci)
     ms_perm = timeit(lambda: ops.permute_values(probs, perm))
     emit("C4", "permute_values [R,nnz]", ms_perm, r * 8 * nnz + 4 * nnz, 0.0, {"replicas_per_gpu": r})
+    rit = torch.argsort(rot[1:] - rot[:-1], descending=True, stable=True).to(torch.int32)
+    ms_t2 = timeit(lambda: ops.spmm(s, s, ops.permute_values(probs, perm), rit, rot, cit, vv))
+    ms_t1 = timeit(lambda: ops.spmm_perm(s, s, probs, perm, rit, rot, cit, vv))
+    emit("C4", "A^T spmm (backward dK/dV): spmm_perm, values read through the cached permutation", ms_t1,
+         r * (4 * nnz + 8 * s * d) + 2 * topo, 2.0 * nnz * d * r,
+         {"replicas_per_gpu": r, "permute_values_then_spmm_ms": round(ms_t2, 4)})
     total = ms_sddmm + ms_soft + ms_spmm
     emit("C4", "attention fwd (3 ops)", total, r * (16 * nnz + 16 * s * d) + 2 * topo + 4 * (2 * s + 1),
          4.0 * nnz * d * r, {"replicas_per_gpu": r, "replicas_total": replicas})

@@ -50,6 +50,7 @@ sparse_softmax_backward = torch_sputnik.sparse_softmax_backward
 csr_transpose_with_perm = torch_sputnik.csr_transpose_with_perm
 permute_values = torch_sputnik.permute_values
 sparse_attention = torch_sputnik.sparse_attention
+spmm_perm = torch_sputnik.spmm_perm
 spmm_many_mask = torch_sputnik.spmm_many_mask
 sddmm_many_mask = torch_sputnik.sddmm_many_mask
 sparse_softmax_many_mask = torch_sputnik.sparse_softmax_many_mask
@@ -60,6 +61,6 @@ launch_count = torch_sputnik.launch_count
 __all__ = [
     "torch_sputnik", "spmm", "left_spmm", "sddmm", "sparse_softmax", "csr_transpose",
     "spmm_bias_relu", "spmm_bias", "sddmm_reduce", "sparse_softmax_scaled", "sparse_softmax_backward",
-    "csr_transpose_with_perm", "permute_values", "sparse_attention", "spmm_many_mask", "sddmm_many_mask",
+    "csr_transpose_with_perm", "permute_values", "sparse_attention", "spmm_perm", "spmm_many_mask", "sddmm_many_mask",
     "sparse_softmax_many_mask", "csr_transpose_many_mask", "set_variant", "launch_count",
 ]

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libtsp.so")
 
 # Every symbol include/tsp.h declares.
 SYMBOLS = (
-    "tsp_version", "tsp_last_error", "tsp_spmm_f32", "tsp_sddmm_f32", "tsp_sddmm_reduce_f32", "tsp_csr_softmax_f32",
+    "tsp_version", "tsp_last_error", "tsp_spmm_f32", "tsp_spmm_perm_f32", "tsp_sddmm_f32", "tsp_sddmm_reduce_f32", "tsp_csr_softmax_f32",
     "tsp_csr_softmax_backward_f32", "tsp_csr_transpose_workspace", "tsp_csr_transpose_f32",
     "tsp_permute_values_f32", "tsp_sparse_attention_supported", "tsp_sparse_attention_f32", "tsp_set_variant",
     "tsp_launch_count",
@@ -29,6 +29,7 @@ def load() -> ctypes.CDLL:
         lib.tsp_version.restype = i
         lib.tsp_last_error.restype = ctypes.c_char_p
         lib.tsp_spmm_f32.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, i, vp, vp]
+        lib.tsp_spmm_perm_f32.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, i, vp, vp]
         lib.tsp_sddmm_f32.argtypes = [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_sddmm_reduce_f32.argtypes = [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_csr_softmax_f32.argtypes = [i, i, i, f, vp, vp, vp, vp, vp]

@@ -28,6 +28,10 @@ struct SpmmArgs {
   const float* bias;  // may be null
   int relu;
   float* out;
+  // value_perm != null: nonzero p takes values[value_perm[p]] -- the CSR arrays describe the
+  // TRANSPOSE of the matrix the values are stored for (perm from tsp_csr_transpose_f32), so a
+  // backward pass multiplies by A^T without materialising the permuted [replicas, nnz] values.
+  const int* value_perm = nullptr;
   // When guard_id != 0 the gather kernel is the fallback of a staged launch: it runs only if the
   // sorted-columns check raised g_unsorted_flag[guard_slot] == guard_id.
   int guard_slot = 0;
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
     const int cnt = min(32, end - base);
     int2 p = make_int2(0, 0);
     if (lane < cnt) {
-      p.x = __float_as_int(__ldg(vals + base + lane));
+      p.x = __float_as_int(__ldg(vals + (a.value_perm ? __ldg(a.value_perm + base + lane) : base + lane)));
       p.y = __ldg(cols + base + lane);
       if (OFF32) p.y = (int)((unsigned)p.y * row_vecs);
     }

@@ -166,7 +166,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
         const int idx = pos[g] + u * LPR + t_lane;
         const bool in = idx < endp[g];
         pc[g][u] = in ? __ldg(cols + idx) : 0x7fffffff;
-        pv[g][u] = in ? __ldg(vals + idx) : 0.f;
+        pv[g][u] = in ? __ldg(vals + (a.value_perm ? __ldg(a.value_perm + idx) : idx)) : 0.f;
       }
   };
   prefetch();
@@ -214,7 +214,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
           const bool tk = c < k1;
           unsigned b2 = 0;
           if (tk) {
-            tile[(c - k0) * R + r_lane] = __ldg(vals + idx);
+            tile[(c - k0) * R + r_lane] = __ldg(vals + (a.value_perm ? __ldg(a.value_perm + idx) : idx));
             b2 = 1u << (c - k0);
           }
           mask |= __reduce_or_sync(kFullMask, b2);

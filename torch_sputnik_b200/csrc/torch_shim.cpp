@@ -67,7 +67,7 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values,
                         const torch::Tensor& row_indices_in, const torch::Tensor& row_offsets,
                         const torch::Tensor& column_indices, const torch::Tensor& dense,
                         const c10::optional<torch::Tensor>& bias, bool relu, bool left,
-                        const char* op) {
+                        const char* op, const c10::optional<torch::Tensor>& value_perm = c10::nullopt) {
   TORCH_CHECK(values.dim() == 1 || values.dim() == 2, "torch_sputnik.", op,
               ": values must have 1 or 2 dimensions");
   TORCH_CHECK(dense.dim() == 2 || dense.dim() == 3, "torch_sputnik.", op,
@@ -102,16 +102,25 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values,
     bias_ptr = bias_t.data_ptr<float>();
   }
 
+  const int* perm_ptr = nullptr;
+  torch::Tensor perm_t;
+  if (value_perm.has_value()) {
+    perm_t = *value_perm;
+    TSP_CHECK_CUDA_I32(perm_t, "value_perm");
+    TORCH_CHECK(perm_t.dim() == 1 && perm_t.size(0) == nnz, "torch_sputnik.", op, ": value_perm must have nnz elements");
+    perm_ptr = perm_t.data_ptr<int>();
+  }
+
   auto options = torch::TensorOptions().dtype(torch::kFloat32).device(values.device());
   // Reference quirk: `spmm` returns 2-D whenever the replica count is 1 (src/spmm_cuda.cu:46);
   // `left_spmm` is always 3-D (src/left_replicated_spmm.cu:30).
   torch::Tensor out = (left || replicas != 1) ? torch::empty({replicas, m, n}, options)
                                               : torch::empty({m, n}, options);
-  check_rc(tsp_spmm_f32((int)m, (int)k, (int)n, (int)nnz, (int)replicas, shared ? 1 : 0,
-                        row_indices.data_ptr<int>(), values.data_ptr<float>(),
-                        row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
-                        dense.data_ptr<float>(), bias_ptr, relu ? 1 : 0, out.data_ptr<float>(),
-                        current_stream()),
+  check_rc(tsp_spmm_perm_f32((int)m, (int)k, (int)n, (int)nnz, (int)replicas, shared ? 1 : 0,
+                             row_indices.data_ptr<int>(), values.data_ptr<float>(), perm_ptr,
+                             row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                             dense.data_ptr<float>(), bias_ptr, relu ? 1 : 0, out.data_ptr<float>(),
+                             current_stream()),
            op);
   return out;
 }
@@ -317,6 +326,14 @@ torch::Tensor permute_values(torch::Tensor values, torch::Tensor perm) {
   return out;
 }
 
+// Extension: spmm with the transposed topology of a cached csr_transpose and the ORIGINAL values
+// (nonzero p reads values[..., perm[p]]): A^T @ dense without the permute_values pass.
+torch::Tensor spmm_perm(int m, int k, torch::Tensor values, torch::Tensor perm, torch::Tensor row_indices,
+                        torch::Tensor row_offsets, torch::Tensor column_indices, torch::Tensor dense) {
+  return spmm_impl(m, k, values, row_indices, row_offsets, column_indices, dense, c10::nullopt, false,
+                   false, "spmm_perm", perm);
+}
+
 // Extension: modules/sparse_attention.py:66-82 in one kernel.  q [R, m, d],
 // k and v [R, n, d] (or 2-D for R = 1) -> [out [R, m, d], lse [R, m]].  Head dimensions the fused
 // kernel does not take go through the three-op chain (lse is then left empty).
@@ -373,6 +390,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("csr_transpose_with_perm", &csr_transpose_with_perm, "csr_transpose + permutation");
   m.def("permute_values", &permute_values, "values[..., perm]");
   m.def("sddmm_reduce", &sddmm_reduce, "sum over replicas of sddmm -> [nnz] (sparse-linear weight gradient)");
+  m.def("spmm_perm", &spmm_perm, "spmm reading values through a permutation (transposed topology, original values)");
   m.def("sparse_attention", &sparse_attention, "fused sddmm -> softmax(scale) -> spmm; returns [out, lse]");
   m.def("spmm_many_mask", &spmm_many_mask, "spmm with one CSR mask per batch element");
   m.def("sddmm_many_mask", &sddmm_many_mask, "sddmm with one CSR mask per batch element");

@@ -86,6 +86,14 @@ int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
                  const int* row_indices, const float* values, const int* row_offsets,
                  const int* column_indices, const float* dense, const float* bias_or_null,
                  int relu, float* out, void* stream_) {
+  return tsp_spmm_perm_f32(m, k, n, nnz, replicas, values_shared, row_indices, values, nullptr, row_offsets,
+                           column_indices, dense, bias_or_null, relu, out, stream_);
+}
+
+int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
+                      const int* row_indices, const float* values, const int* value_perm_or_null,
+                      const int* row_offsets, const int* column_indices, const float* dense,
+                      const float* bias_or_null, int relu, float* out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
     return invalid("tsp_spmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k, n,
@@ -106,6 +114,7 @@ int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
   a.bias = bias_or_null;
   a.relu = relu;
   a.out = out;
+  a.value_perm = value_perm_or_null;
 
   const int variant = g_spmm_variant.load();
   const bool vec4_ok = (n % 4 == 0) && aligned16(dense) && aligned16(out);

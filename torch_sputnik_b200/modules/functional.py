@@ -87,9 +87,9 @@ class Spmm(torch.autograd.Function):
                                         dense.contiguous())
         if ctx.needs_input_grad[6]:
             t = TransposedTopology.get(m, k, row_offsets, column_indices)
-            values_t = ops.permute_values(values.contiguous(), t.perm)
-            grad_dense = ops.spmm(k, m, values_t, t.row_indices, t.row_offsets, t.column_indices,
-                                  grad_output)
+            # A^T @ dC on the cached transposed topology, values read through the permutation
+            grad_dense = ops.spmm_perm(k, m, values.contiguous(), t.perm, t.row_indices, t.row_offsets,
+                                       t.column_indices, grad_output)
             grad_dense = grad_dense.reshape(dense.shape)
         return None, None, grad_values, None, None, None, grad_dense
 
@@ -116,9 +116,8 @@ class Sddmm(torch.autograd.Function):
                                 rhs.contiguous()).reshape(lhs.shape)
         if ctx.needs_input_grad[6]:
             t = TransposedTopology.get(m, n, row_offsets, column_indices)
-            grad_t = ops.permute_values(grad_output, t.perm)
-            grad_rhs = ops.spmm(n, m, grad_t, t.row_indices, t.row_offsets, t.column_indices,
-                                lhs.contiguous()).reshape(rhs.shape)
+            grad_rhs = ops.spmm_perm(n, m, grad_output, t.perm, t.row_indices, t.row_offsets, t.column_indices,
+                                     lhs.contiguous()).reshape(rhs.shape)
         return None, None, None, None, None, grad_lhs, grad_rhs
 
 
