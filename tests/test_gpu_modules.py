@@ -115,6 +115,37 @@ def test_sparse_attention_matches_dense_masked_attention(dev):
         torch.testing.assert_close(got.double(), want, rtol=1e-4, atol=1e-5)
 
 
+@pytest.mark.parametrize("heads", [1, 3])
+def test_many_mask_attention_matches_dense_masked_attention(dev, heads):
+    """One sparse mask per batch element (the reference's tests/test_attention_many_masks.py
+    set-up: alternating sparsities, so every mask has another nnz): forward through the
+    ``*_many_mask`` ops, forward + backward through the per-mask autograd Functions, both against
+    dense masked attention in fp64."""
+    from torch_sputnik_b200.modules import ManyMaskTopology, many_mask_attention
+    torch.manual_seed(4)
+    b, h, s, d = 3, heads, 96, 64
+    masks = torch.stack([torch.rand(s, s, device=dev) >= (0.5 if i % 2 else 0.8) for i in range(b)])
+    masks |= torch.eye(s, dtype=torch.bool, device=dev)         # no empty row (dense softmax needs one entry)
+    topo = ManyMaskTopology(masks)
+    assert len(set(topo.nonzeros.tolist())) > 1
+    scale = 1.0 / math.sqrt(d)
+    q, k, v = (torch.randn(b, h, s, d, device=dev, requires_grad=True) for _ in range(3))
+    out = many_mask_attention(q, k, v, topo, scale)
+    g = torch.randn_like(out)
+    out.backward(g)
+    with torch.no_grad():
+        fwd_only = many_mask_attention(q, k, v, topo, scale)     # the *_many_mask op path
+    q64, k64, v64 = (t.detach().double().requires_grad_(True) for t in (q, k, v))
+    scores = (q64 @ k64.transpose(-2, -1)) * scale
+    scores = scores.masked_fill(~masks[:, None], float("-inf"))
+    ref = (torch.softmax(scores, dim=-1) @ v64).reshape(b * h, s, d)
+    ref.backward(g.double())
+    torch.testing.assert_close(out.double(), ref, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(fwd_only.double(), ref, rtol=1e-4, atol=1e-5)
+    for got, want in ((q.grad, q64.grad), (k.grad, k64.grad), (v.grad, v64.grad)):
+        torch.testing.assert_close(got.double(), want, rtol=1e-4, atol=1e-5)
+
+
 def test_sparse_attention_module_forward_backward_runs(dev):
     from torch_sputnik_b200.modules import SparseAttention
     torch.manual_seed(2)

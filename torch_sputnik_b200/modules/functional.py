@@ -76,6 +76,9 @@ class Spmm(torch.autograd.Function):
         row_indices, row_offsets, column_indices = ctx.topology
         values, dense = ctx.saved_tensors
         grad_output = grad_output.contiguous()
+        if grad_output.dim() != dense.dim():
+            # one replica: the forward returned [m, n] for a [1, k, n] operand (src/spmm_cuda.cu:46)
+            grad_output = grad_output.reshape(dense.shape[:-2] + grad_output.shape[-2:])
         grad_values = grad_dense = None
         if ctx.needs_input_grad[2]:
             # dA = (dC @ B^T) sampled at the pattern; sddmm wants the right operand as [k, n].
@@ -170,3 +173,56 @@ class SparseLinearFunction(torch.autograd.Function):
             grad_dense = ops.left_spmm(k, m, values_t, t.row_indices, t.row_offsets,
                                        t.column_indices, grad_output).reshape(dense.shape)
         return None, None, grad_values, None, None, None, grad_dense
+
+
+class ManyMaskTopology:
+    """``b`` CSR masks of one shape (one per batch element) packed the way the ``*_many_mask`` ops
+    take them (csrc/many_mask.inc; tests/transformer/utils.py:20-40 of the reference builds the same
+    from a ``[b, m, n]`` mask): stacked ``row_indices [b, m]`` / ``row_offsets [b, m+1]`` with LOCAL
+    offsets, concatenated ``column_indices``, ``nonzeros`` on the CPU."""
+
+    def __init__(self, masks: torch.Tensor):
+        assert masks.dim() == 3, "masks must be [b, m, n]"
+        self.b, self.m, self.n = masks.shape
+        parts = [dense_to_sparse(masks[i].to(torch.float32)) for i in range(self.b)]
+        self.row_indices = torch.stack([p[1] for p in parts]).contiguous()
+        self.row_offsets = torch.stack([p[2] for p in parts]).contiguous()
+        self.column_indices = torch.cat([p[3] for p in parts]).contiguous()
+        self.nonzeros = torch.tensor([p[3].numel() for p in parts], dtype=torch.int64)
+        self._parts = [(p[1], p[2], p[3]) for p in parts]
+
+    def mask(self, i: int):
+        """(row_indices, row_offsets, column_indices) of mask ``i`` for the single-mask ops."""
+        return self._parts[i]
+
+
+def many_mask_attention(query, key, value, topo: ManyMaskTopology, scale: float):
+    """softmax(scale * Q K^T restricted to mask[batch]) V with one sparse mask per batch element;
+    ``query`` / ``key`` / ``value`` are [B, H, S, D] with B == topo.b.  Returns [B * H, S, D].
+
+    Without autograd this is three ``*_many_mask`` calls.  With autograd every mask goes through
+    the single-mask Functions above (same kernels, one launch per mask either way), which carry
+    the backward passes -- the reference's many-mask softmax gradient is a placeholder
+    (tests/transformer/functions.py:105-115)."""
+    b, h, s, d = query.shape
+    assert b == topo.b and s == topo.m
+    q3, k3, v3 = (t.reshape(b * h, -1, d).contiguous() for t in (query, key, value))
+    if not (torch.is_grad_enabled() and (q3.requires_grad or k3.requires_grad or v3.requires_grad)):
+        scores = ops.sddmm_many_mask(b, topo.m, topo.n, topo.nonzeros, topo.row_indices, topo.row_offsets,
+                                     topo.column_indices, q3, k3)
+        # the scale is folded into the scores' left operand: softmax(scale * x) has no many-mask entry
+        if scale != 1.0:
+            scores = scores * scale
+        probs = ops.sparse_softmax_many_mask(b, topo.m, topo.nonzeros, scores, topo.row_indices,
+                                             topo.row_offsets, topo.column_indices)
+        return ops.spmm_many_mask(b, topo.m, topo.n, topo.nonzeros, probs, topo.row_indices, topo.row_offsets,
+                                  topo.column_indices, v3)
+    outs = []
+    for i in range(b):
+        ri, ro, ci = topo.mask(i)
+        sl = slice(i * h, (i + 1) * h)
+        scores = Sddmm.apply(topo.m, topo.n, ri, ro, ci, q3[sl], k3[sl])
+        probs = CsrSoftmax.apply(scores, ri, ro, ci, scale)
+        out = Spmm.apply(topo.m, topo.n, probs, ri, ro, ci, v3[sl])
+        outs.append(out.reshape(h, topo.m, d))
+    return torch.cat(outs, dim=0)
