@@ -269,7 +269,9 @@ def test_sddmm_rows_empty_rows_and_unsorted(ops, dev, variant):
     (256, 320, 512, 0.1, 4),      # sampled kernel, replica loop folded into the k loop
     (256, 320, 512, 0.5, 3),      # tiled kernel
     (130, 70, 96, 0.3, 5),        # neither staged kernel applies: scratch + reduce
-    (300, 513, 260, 0.05, 2), (128, 128, 256, 0.1, 1)])
+    (300, 513, 260, 0.05, 2), (128, 128, 256, 0.1, 1),
+    (512, 512, 512, 0.1, 4), (512, 2048, 512, 0.1, 4),   # C5 layer shapes: 16 / 64 tiles -> split-K CTAs + partial sums
+    (384, 256, 4096, 0.1, 1)])                            # one replica, long k: split-K on the 2-D path
 def test_sddmm_reduce_sums_over_replicas(ops, dev, m, n, k, density, reps):
     """sddmm_reduce == sddmm(...).sum(0): the sparse-linear weight gradient (modules/sparse_linear.py:44
     + autograd's broadcast sum) without the [R, nnz] intermediate."""

@@ -264,7 +264,7 @@ def test_spmm_narrow_operand_wide_ctas(ops, dev, m, k, n, density, reps, warps):
 
 @pytest.mark.parametrize("m,k,n,density,reps,variant", [
     (300, 260, 64, 0.1, 3, 0),       # attention backward shape class: gather kernel, 2-D values
-    (256, 512, 256, 0.5, 2, 2),      # staged kernel reads its candidates through the permutation too
+    (256, 512, 256, 0.5, 2, 2),      # staged forced: a permuted call still goes through the gather kernel
     (130, 90, 33, 0.3, 1, 0),        # scalar path, 1-D values
 ])
 def test_spmm_perm_multiplies_by_the_transpose(ops, dev, m, k, n, density, reps, variant):
@@ -285,7 +285,10 @@ def test_spmm_perm_multiplies_by_the_transpose(ops, dev, m, k, n, density, reps,
         explicit = ops.spmm(k, m, ops.permute_values(tv, perm), rit, rot, cit, td)
     finally:
         ops.set_variant("spmm", prev)
-    assert torch.equal(got, explicit)
+    if variant == 0:
+        assert torch.equal(got, explicit)       # same (gather) kernel on both sides
+    else:
+        torch.testing.assert_close(got, explicit, rtol=1e-5, atol=1e-5)
     got = got.cpu().numpy().reshape(lead + (k, n))
     for r in range(reps):
         v_r, d_r = (vals[r], dense[r]) if reps > 1 else (vals, dense)

@@ -74,9 +74,8 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   if (j0 >= a.nnz) return;
   const int rep = blockIdx.y;
   const int k = a.k;
-
-  const float* __restrict__ lhs = a.lhs + (size_t)rep * a.m * k;
-  const float* __restrict__ rhs = a.rhs + (size_t)rep * a.n * k;
+  // reduce_reps > 0: one output vector, the replica loop runs here (grid.y == 1)
+  const int nrep = a.reduce_reps > 0 ? a.reduce_reps : 1;
 
   const int grp = lane / LPN;
   const int sub = lane % LPN;
@@ -96,6 +95,9 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   for (int i = 0; i < NPG; ++i) acc[i] = 0.f;
 
   // Group g owns nonzeros j0 + g*NPG + i, i in [0, NPG).
+  for (int rr = 0; rr < nrep; ++rr) {
+  const float* __restrict__ lhs = a.lhs + (size_t)(rep + rr) * a.m * k;
+  const float* __restrict__ rhs = a.rhs + (size_t)(rep + rr) * a.n * k;
   for (int kk = 0; kk < k; kk += KSTEP) {
     const int kofs = kk + sub * VEC;
     const bool kin = kofs < k;  // VEC == 4 implies k % 4 == 0, so a vector is all-in or all-out
@@ -130,6 +132,7 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
       }
     }
   }
+  }
 
   transpose_reduce<LPN>(acc, lane);
   const int j = j0 + grp * NPG + sub;
@@ -152,7 +155,7 @@ reduce_replicas_kernel(const float* __restrict__ scratch, int nnz, int replicas,
 template <int VEC, int LPN>
 inline void launch_sddmm_gather(const SddmmArgs& a, int replicas, cudaStream_t stream) {
   constexpr int WARPS = 4;
-  dim3 grid(ceil_div(ceil_div(a.nnz, 32), WARPS), replicas, 1);
+  dim3 grid(ceil_div(ceil_div(a.nnz, 32), WARPS), a.reduce_reps > 0 ? 1 : replicas, 1);
   sddmm_gather_kernel<VEC, LPN, WARPS><<<grid, WARPS * 32, 0, stream>>>(a);
 }
 

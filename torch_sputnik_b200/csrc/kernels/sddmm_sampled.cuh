@@ -26,6 +26,9 @@
 // Precondition: ascending columns per row (device-checked; gather fallback otherwise), k % 4 == 0,
 // 16-byte aligned operands.
 #pragma once
+#include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 #include "sddmm_tiled.cuh"
 
 namespace tsp {
@@ -42,10 +45,24 @@ struct SddmmSampledCfg {
 
 // starts[row * (nb + 1) + b] = first flat index in row `row` whose column is >= b * bn
 // (b == nb gives the row's end).  Needs ascending columns.
+// One launch for both pre-passes of the sampled kernel: blocks [0, check_blocks) are
+// csr_check_sorted_kernel, the rest csr_block_starts_kernel (small masks are bound by the number
+// of launches per call, not by the work in them).
 __global__ void __launch_bounds__(256)
-csr_block_starts_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m, int nb,
-                        int bn, int* __restrict__ starts) {
-  const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+csr_prepare_sampled_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m, int nb, int bn,
+                           int* __restrict__ starts, int check_blocks, int slot, unsigned call_id) {
+  if ((int)blockIdx.x < check_blocks) {
+    const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int nwarps = (check_blocks * 256) >> 5;
+    bool bad = false;
+    for (int row = warp; row < m; row += nwarps) {
+      const int beg = __ldg(row_offsets + row), end = __ldg(row_offsets + row + 1);
+      for (int j = beg + lane; j + 1 < end; j += 32) bad |= __ldg(cols + j) >= __ldg(cols + j + 1);
+    }
+    if (__any_sync(kFullMask, bad) && lane == 0) g_unsorted_flag[slot] = call_id;
+    return;
+  }
+  const long long t = (long long)(blockIdx.x - check_blocks) * 256 + threadIdx.x;
   if (t >= (long long)m * (nb + 1)) return;
   const int row = (int)(t / (nb + 1)), b = (int)(t % (nb + 1));
   int lo = __ldg(row_offsets + row), hi = __ldg(row_offsets + row + 1);
@@ -77,7 +94,7 @@ template <class Cfg, int NB_LO>
 __global__ void __launch_bounds__(Cfg::THREADS, 2)
 sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
                      const int* __restrict__ starts, const __grid_constant__ CUtensorMap tm_lhs,
-                     const __grid_constant__ CUtensorMap tm_rhs) {
+                     const __grid_constant__ CUtensorMap tm_rhs, const int ksplit) {
   constexpr int BM = Cfg::BM, BK = Cfg::BK, P = Cfg::P, STAGES = Cfg::STAGES, CAP = Cfg::CAP;
   if (g_unsorted_flag[guard.slot] == guard.call_id) return;
 
@@ -99,7 +116,12 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
   const int rb = blockIdx.x / nb, cb = blockIdx.x % nb;
   const int rep = blockIdx.y;
   const int ksteps1 = (a.k + BK - 1) / BK;                                   // k-slabs of one replica
-  const int ksteps = a.reduce_reps > 0 ? ksteps1 * a.reduce_reps : ksteps1;   // slabs per tile round
+  const int ksteps_all = a.reduce_reps > 0 ? ksteps1 * a.reduce_reps : ksteps1;   // slabs per tile round
+  // split-K (small masks: fewer tiles than SMs): grid.z CTAs share a tile, each takes a contiguous
+  // range of the slabs and writes its partial sums to slice (rep * ksplit + z) of `out`, which is
+  // then scratch that reduce_replicas_kernel sums.
+  const int kbeg = (int)((long long)ksteps_all * blockIdx.z / ksplit);
+  const int ksteps = (int)((long long)ksteps_all * (blockIdx.z + 1) / ksplit) - kbeg;
 
   if (tid == 0) {
 #pragma unroll
@@ -149,7 +171,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
   if (total == 0) return;
 
   const int* __restrict__ cols = a.column_indices;
-  float* __restrict__ out = a.out + (size_t)rep * a.nnz;
+  float* __restrict__ out = a.out + ((size_t)rep * ksplit + blockIdx.z) * a.nnz;
   const int c0 = cb * bn;
   int q = 0, q_base = 0;  // slabs consumed so far by this CTA (ring position carries across rounds)
 
@@ -193,7 +215,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
       const int st = qq % STAGES, use = qq / STAGES;
       if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
       unsigned char* const dst = ring + (size_t)st * stage_bytes;
-      const int kq = (qq - q_base) % ksteps;
+      const int kq = kbeg + (qq - q_base);
       const int ks = kq % ksteps1, rr = a.reduce_reps > 0 ? kq / ksteps1 : rep;
       mbar_arrive_expect_tx(full + st, (unsigned)stage_bytes);
       tma_load_3d(dst, &tm_lhs, ks * BK, rb * BM, rr, full + st);
@@ -273,6 +295,15 @@ inline bool sddmm_sampled_applicable(const SddmmArgs& a, int replicas) {
   return 2.0 * a.nnz * a.k * replicas >= 5.0e7;
 }
 
+// Split-K factor: when the mask has fewer tiles than the GPU has CTA slots (sparse-linear weight
+// gradients of small layers: a 512 x 512 mask is 16 tiles), grid.z CTAs share a tile; every CTA
+// keeps >= 8 slabs.
+inline int sddmm_sampled_ksplit(long long tiles, int grid_reps, int ksteps_all) {
+  if (grid_reps != 1 || tiles >= sm_count()) return 1;
+  long long ks = std::min<long long>(2LL * sm_count() / tiles, ksteps_all / 8);
+  return (int)std::max<long long>(1, std::min<long long>(ks, 64));
+}
+
 template <class Cfg, int NB_LO>
 inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_t stream,
                                    const StagedGuard& guard, int bn) {
@@ -291,9 +322,10 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
   cudaError_t e = cudaMallocAsync(&ws, (size_t)a.m * (nb + 1) * 4 + 256, stream);
   if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled scratch)");
   int* starts = static_cast<int*>(ws);
-  csr_block_starts_kernel<<<ceil_div((long long)a.m * (nb + 1), 256), 256, 0, stream>>>(
-      a.row_offsets, a.column_indices, a.m, nb, bn, starts);
-  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (block starts)");
+  const int check_blocks = min(ceil_div(a.m, 8), 4 * sm_count());
+  csr_prepare_sampled_kernel<<<check_blocks + (int)ceil_div((long long)a.m * (nb + 1), 256), 256, 0, stream>>>(
+      a.row_offsets, a.column_indices, a.m, nb, bn, starts, check_blocks, guard.slot, guard.call_id);
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sorted check + block starts)");
   CUtensorMap tm_lhs, tm_rhs;
   if (!encode_rowmajor_map_plain(&tm_lhs, a.lhs, replicas, a.m, a.k, Cfg::BM) ||
       !encode_rowmajor_map_plain(&tm_rhs, a.rhs, replicas, a.n, a.k, bn)) {
@@ -301,9 +333,32 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
     set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
     return 2;
   }
-  dim3 grid(row_blocks * nb, a.reduce_reps > 0 ? 1 : replicas);
-  sddmm_sampled_kernel<Cfg, NB_LO><<<grid, Cfg::THREADS, smem, stream>>>(a, guard, nb, bn, starts, tm_lhs, tm_rhs);
+  const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;
+  // Split-K when the mask has fewer tiles than the GPU has CTA slots (sparse-linear weight
+  // gradients of small layers: a 512 x 512 mask is 16 tiles): every CTA keeps >= 8 slabs.
+  const int ksteps_all = ceil_div(a.k, Cfg::BK) * (a.reduce_reps > 0 ? a.reduce_reps : 1);
+  const long long tiles = (long long)row_blocks * nb * grid_reps;
+  const int ksplit = sddmm_sampled_ksplit(tiles, grid_reps, ksteps_all);
+  SddmmArgs b = a;
+  float* partial = nullptr;
+  if (ksplit > 1) {
+    e = cudaMallocAsync(reinterpret_cast<void**>(&partial), sizeof(float) * (size_t)ksplit * a.nnz, stream);
+    if (e != cudaSuccess) {
+      cudaFreeAsync(ws, stream);
+      return cuda_fail(e, "tsp_sddmm_f32 (split-K scratch)");
+    }
+    b.out = partial;
+  }
+  dim3 grid(row_blocks * nb, grid_reps, ksplit);
+  sddmm_sampled_kernel<Cfg, NB_LO><<<grid, Cfg::THREADS, smem, stream>>>(b, guard, nb, bn, starts, tm_lhs, tm_rhs, ksplit);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sampled)");
+  if (ksplit > 1) {
+    // (with unsorted columns the sampled kernel exits and this sums garbage; the guarded gather
+    // fallback queued behind by the caller then rewrites every element of out)
+    reduce_replicas_kernel<<<ceil_div(a.nnz, 256), 256, 0, stream>>>(partial, a.nnz, ksplit, a.out, 0, 0u);
+    TSP_CHECK_LAUNCH("tsp_sddmm_f32 (split-K sum)");
+    cudaFreeAsync(partial, stream);
+  }
   cudaFreeAsync(ws, stream);
   return 0;
 }
@@ -324,13 +379,17 @@ inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream
 
 // Tile width: among the multiples of 8 columns (<= 256, <= n) whose expected nonzero count plus
 // three standard deviations fits the 32*P register slots of a CTA, the one with the lowest
-// modelled time = waves of 2 CTAs per SM x per-slab cost, where the per-slab cost is the larger of
-// the shared-memory wavefronts (4 clk per slot per warp) and the operand staging traffic.
+// modelled time = waves of 2 CTAs per SM x (slabs per CTA x per-slab cost + the per-tile set-up),
+// where the per-slab cost is the larger of the shared-memory wavefronts (4 clk per slot per warp)
+// and the operand staging traffic, and the set-up (row ranges, dealing the nonzeros to slots,
+// filling the ring, the final butterfly and scatter) is ~6 us + 64 clk per slot -- it decides the
+// width for small masks, where a CTA sees only a few slabs.
 template <class Cfg>
 inline int sddmm_sampled_tile_width(const SddmmArgs& a, int replicas) {
   const double density = (double)a.nnz / ((double)a.m * (double)a.n);
   const int row_blocks = ceil_div(a.m, Cfg::BM);
   const int slots = 2 * sm_count();
+  const int ksteps_all = ceil_div(a.k, Cfg::BK) * (a.reduce_reps > 0 ? a.reduce_reps : 1);
   int best = 16;
   double best_cost = 1e300;
   const int bn_max = a.n / 8 * 8 < 256 ? a.n / 8 * 8 : 256;
@@ -341,9 +400,12 @@ inline int sddmm_sampled_tile_width(const SddmmArgs& a, int replicas) {
     const int per = (int)ceil(need / Cfg::GROUPS);
     const int batches = (per + 3) / 4;
     const long long tiles = (long long)row_blocks * ceil_div(a.n, bn) * replicas;
-    const double waves = (double)((tiles + slots - 1) / slots);
+    const int ksplit = sddmm_sampled_ksplit(tiles, replicas, ksteps_all);
+    const double waves = (double)((tiles * ksplit + slots - 1) / slots);
     const double lsu = 64.0 * (4.0 * batches + 2.0), mem = 4.0 * (Cfg::BM + bn);
-    const double cost = waves * ((lsu > mem ? lsu : mem) + 200.0);
+    const double slab = (lsu > mem ? lsu : mem) + 200.0;
+    const double setup = 12000.0 + 64.0 * per;
+    const double cost = waves * (slab * ceil_div(ksteps_all, ksplit) + setup);
     if (cost < best_cost) {
       best_cost = cost;
       best = bn;
@@ -359,9 +421,6 @@ inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t s
   if (id == 0) id = g_call_counter.fetch_add(1) + 1;
   StagedGuard guard{(int)(id % kFlagSlots), id};
   *guard_out = guard;
-  csr_check_sorted_kernel<<<min(ceil_div(a.m, 8), 4 * sm_count()), 256, 0, stream>>>(
-      a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
-  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sorted check)");
   const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;   // tiles are spread over this many grid.y slices
   if (p_override == 48) {
     using Cfg = SddmmSampledCfg<48, 2>;
@@ -370,6 +429,7 @@ inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t s
   }
   using Cfg = SddmmSampledCfg<56, 2>;
   const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, grid_reps);
+  if (getenv("TSP_DEBUG")) fprintf(stderr, "[tsp] sampled m=%d n=%d k=%d reps=%d bn=%d\n", a.m, a.n, a.k, a.reduce_reps, bn);
   return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
 }
 

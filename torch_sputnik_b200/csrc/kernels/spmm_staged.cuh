@@ -166,7 +166,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
         const int idx = pos[g] + u * LPR + t_lane;
         const bool in = idx < endp[g];
         pc[g][u] = in ? __ldg(cols + idx) : 0x7fffffff;
-        pv[g][u] = in ? __ldg(vals + (a.value_perm ? __ldg(a.value_perm + idx) : idx)) : 0.f;
+        pv[g][u] = in ? __ldg(vals + idx) : 0.f;
       }
   };
   prefetch();
@@ -214,7 +214,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
           const bool tk = c < k1;
           unsigned b2 = 0;
           if (tk) {
-            tile[(c - k0) * R + r_lane] = __ldg(vals + (a.value_perm ? __ldg(a.value_perm + idx) : idx));
+            tile[(c - k0) * R + r_lane] = __ldg(vals + idx);
             b2 = 1u << (c - k0);
           }
           mask |= __reduce_or_sync(kFullMask, b2);
@@ -318,6 +318,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
 
 // ------------------------------------------------------------------------------------ host
 inline bool spmm_staged_applicable(const SpmmArgs& a, int replicas) {
+  if (a.value_perm != nullptr) return false;   // the staged kernel sits at its register budget; permuted values go through the gather kernel
   if (a.n % 4 != 0 || a.n < 96) return false;
   if (!aligned16(a.dense) || !aligned16(a.out)) return false;
   if (a.k < 64 || a.nnz == 0) return false;

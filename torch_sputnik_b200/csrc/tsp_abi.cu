@@ -191,32 +191,31 @@ static int sddmm_impl(int m, int k, int n, int nnz, int replicas, const int* row
     a.reduce_reps = replicas;
     StagedGuard guard;
     int rc = -1;
-    if (dens >= 0.22 && sddmm_tiled_applicable(a, replicas)) rc = launch_sddmm_tiled(a, replicas, stream, &guard, false);
+    const int forced = g_sddmm_variant.load();   // 1: no staged kernel (benchmark knob)
+    if (forced == 1) rc = -1;
+    else if (dens >= 0.22 && sddmm_tiled_applicable(a, replicas)) rc = launch_sddmm_tiled(a, replicas, stream, &guard, false);
     else if (dens >= 0.015 && sddmm_sampled_applicable(a, replicas))
       rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load(), g_sddmm_p.load());
     if (rc > 0) return rc;
-    float* scratch = nullptr;
-    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&scratch), sizeof(float) * (size_t)replicas * nnz, stream);
-    if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_reduce_f32 (scratch)");
-    int rc2;
     if (rc == 0) {
       // The staged kernel wrote out[] unless the columns turned out unsorted; in that case the
-      // guarded gather + reduce below (which exit at once otherwise) redo the work.
+      // guarded gather kernel below (which exits at once otherwise) redoes the work, with the
+      // replica loop inside it.
       SddmmArgs f = a;
-      f.reduce_reps = 0;
-      f.out = scratch;
       f.guard_slot = guard.slot;
       f.guard_id = guard.call_id;
       launch_sddmm_gather_any(f, replicas, stream);
-      g_launches.fetch_add(1, std::memory_order_relaxed);
-      rc2 = cudaGetLastError() == cudaSuccess ? TSP_OK : TSP_ERR_CUDA;
-    } else {
-      rc2 = sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, scratch,
-                       stream_, false);
+      TSP_CHECK_LAUNCH("tsp_sddmm_reduce_f32 (gather fallback)");
+      return TSP_OK;
     }
+    // no staged kernel applies: [replicas, nnz] into stream-ordered scratch, then the sum
+    float* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&scratch), sizeof(float) * (size_t)replicas * nnz, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_reduce_f32 (scratch)");
+    int rc2 = sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, scratch,
+                         stream_, false);
     if (rc2 == TSP_OK) {
-      reduce_replicas_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(scratch, nnz, replicas, out,
-                                                                     rc == 0 ? guard.slot : 0, rc == 0 ? guard.call_id : 0u);
+      reduce_replicas_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(scratch, nnz, replicas, out, 0, 0u);
       g_launches.fetch_add(1, std::memory_order_relaxed);
       if (cudaGetLastError() != cudaSuccess) rc2 = TSP_ERR_CUDA;
     }
