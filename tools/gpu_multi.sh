@@ -8,5 +8,5 @@ nvidia-smi -L > gpurun_out/smi_n$N.txt
 timeout 900 $TR bench.py --gpus $N --steps 5 --warmup 3 --no-cpu-baseline --no-ref-kernel > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"; tail -2 gpurun_out/bench_n$N.err
 timeout 900 $TR tools/bench_configs.py --config c4 > gpurun_out/configs_c4_n$N.jsonl 2> gpurun_out/configs_c4_n$N.err; echo "c4 rc=$?"; tail -2 gpurun_out/configs_c4_n$N.err
 timeout 900 $TR tools/bench_configs.py --config c3 > gpurun_out/configs_c3_n$N.jsonl 2> gpurun_out/configs_c3_n$N.err; echo "c3 rc=$?"; tail -2 gpurun_out/configs_c3_n$N.err
-timeout 900 $TR tools/train_dp_transformer.py --steps 10 > gpurun_out/c5_n$N.json 2> gpurun_out/c5_n$N.err; echo "c5 rc=$?"; tail -2 gpurun_out/c5_n$N.err
+timeout 120 $TR tools/train_dp_transformer.py --steps 10 > gpurun_out/c5_n$N.json 2> gpurun_out/c5_n$N.err; echo "c5 rc=$?"; tail -2 gpurun_out/c5_n$N.err
 cat gpurun_out/c5_n$N.json

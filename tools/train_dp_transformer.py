@@ -144,6 +144,15 @@ def main():
             "loss_first_last": [round(losses[0], 4), round(losses[-1], 4)]}) + "\n")
         real_out.flush()
     if world > 1:
+        torch.cuda.synchronize()
+        if args.graph:
+            # A captured graph holds NCCL work: release it before the communicator goes away, and leave without the
+            # interpreter's teardown -- with the graph alive, barrier + destroy_process_group did not return on 8 GPUs
+            # (the result line above had been written; the run sat in teardown until the job limit).
+            graph.reset()
+            del graph
+            sys.stderr.flush()
+            os._exit(0)
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
 

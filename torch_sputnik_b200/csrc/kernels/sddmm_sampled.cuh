@@ -26,8 +26,6 @@
 // Precondition: ascending columns per row (device-checked; gather fallback otherwise), k % 4 == 0,
 // 16-byte aligned operands.
 #pragma once
-#include <cstdio>
-#include <cstdlib>
 #include <algorithm>
 #include "sddmm_tiled.cuh"
 
@@ -429,7 +427,6 @@ inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t s
   }
   using Cfg = SddmmSampledCfg<56, 2>;
   const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, grid_reps);
-  if (getenv("TSP_DEBUG")) fprintf(stderr, "[tsp] sampled m=%d n=%d k=%d reps=%d bn=%d\n", a.m, a.n, a.k, a.reduce_reps, bn);
   return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
 }
 
