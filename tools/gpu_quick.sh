@@ -1,4 +1,5 @@
 #!/bin/bash
+# scratch: the command of the moment for a single `gpurun -- 'bash tools/gpu_quick.sh'`
 set -u
-python bench.py --steps 5 --no-cpu-baseline --no-ref-kernel 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], [ (c['op'],c['density'],c['ms']) for c in d['cases']])"
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
