@@ -149,3 +149,24 @@ def test_generator_semantics():
     np.testing.assert_array_equal(a.column_indices, b.column_indices)
     assert random_csr(8, 8, 0.0, seed=1).nnz == 0
     assert random_csr(8, 8, 1.0, seed=1).nnz == 64
+
+
+def test_attention_chain_oracle_vs_dense_masked_attention():
+    """The checker of tests/test_gpu_attention.py (oracle sddmm -> softmax(scale) -> spmm) against
+    dense masked softmax attention in fp64 (modules/sparse_attention.py:66-82 semantics)."""
+    import torch
+    from oracle import cpu as ocpu
+    from oracle.csr import dense_operand, from_dense_mask
+    rng = np.random.default_rng(3)
+    m, n, d, scale = 40, 56, 32, 0.2
+    mask = rng.random((m, n)) < 0.3
+    mask[:, 0] = True                                   # no empty row: the dense softmax needs one entry
+    a = from_dense_mask(mask, seed=1)
+    q, k, v = dense_operand((m, d), 1, "pm1"), dense_operand((n, d), 2, "pm1"), dense_operand((n, d), 3, "pm1")
+    s = ocpu.sddmm(m, n, a.row_offsets, a.column_indices, q, k)
+    p = ocpu.csr_softmax(s, a.row_offsets, scale)
+    out = ocpu.spmm(m, n, p, a.row_offsets, a.column_indices, v)
+    scores = torch.from_numpy(q).double() @ torch.from_numpy(k).double().T * scale
+    scores = scores.masked_fill(~torch.from_numpy(mask), float("-inf"))
+    ref = torch.softmax(scores, dim=-1) @ torch.from_numpy(v).double()
+    np.testing.assert_allclose(out, ref.numpy(), rtol=2e-6, atol=2e-6)
