@@ -5,9 +5,17 @@
  * every entry point below replaces one call the reference's PyTorch binding makes
  * into libsputnik / cuSPARSE.  All pointers are DEVICE pointers (fp32 values, int32
  * indices, row-major dense operands), all launches are asynchronous on `stream`
- * (a cudaStream_t passed as void*), no entry point synchronises, allocates or keeps
- * state.  Return value: 0 on success, non-zero on error; tsp_last_error() returns a
- * thread-local message for the last non-zero return.
+ * (a cudaStream_t passed as void*) and no entry point synchronises the stream.
+ * State and allocation: the plain entry points (tsp_spmm_f32, tsp_sddmm_f32, ...) keep no state;
+ * those that need a view of the topology (the staged SpMM / SDDMM kernels: a sortedness word,
+ * block starts, occupancy bitmaps) or split-K partial sums take it from STREAM-ORDERED scratch
+ * (cudaMallocAsync / cudaFreeAsync on `stream`, no synchronisation).  The tsp_plan_* entry points
+ * keep that topology state in a caller-owned handle instead: tsp_plan_create and the first use of
+ * a view allocate with cudaMalloc (once per topology), after which a planned call allocates
+ * nothing and launches only the operator's own kernel.
+ * Operands are assumed FINITE where noted (tsp_spmm_f32).
+ * Return value: 0 on success, non-zero on error; tsp_last_error() returns a thread-local message
+ * for the last non-zero return.
  *
  * "replicas": the reference loops on the host over the leading dimension of 3-D
  * operands and launches one kernel per replica (src/spmm_cuda.cu:48-57).  Here the
@@ -37,7 +45,7 @@
 extern "C" {
 #endif
 
-#define TSP_VERSION 1
+#define TSP_VERSION 2
 
 /* Error codes (also the return values). */
 #define TSP_OK 0
@@ -62,6 +70,9 @@ const char* tsp_last_error(void);
  *   row row_indices[b]).  It may be NULL (identity).  Results do not depend on it.
  *   bias_or_null: [m] fp32 indexed by OUTPUT ROW (cuda_spmm.cu.cc:267-277), or NULL.
  *   relu is honoured with or without bias.
+ *   Non-finite operands: a row's result only ever involves the dense rows the row's own nonzeros
+ *   name (as in the reference, cuda_spmm.cu.cc:224-238) -- an Inf/NaN in dense row c reaches
+ *   exactly the output rows that hold a nonzero in column c, whichever kernel variant runs.
  */
 int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
                  const int* row_indices, const float* values, const int* row_offsets,
@@ -147,6 +158,7 @@ int tsp_sparse_attention_f32(int m, int n, int d, int nnz, int replicas, float s
  *   values_t[replicas, nnz], row_offsets_t[n+1], column_indices_t[nnz] are fully written.
  *   perm_or_null: if non-NULL receives perm[nnz] with values_t[p] = values[perm[p]]
  *   (lets a caller cache the permutation of a static topology).
+ *   replicas == 0: topology only (values / values_t may be NULL).
  *   workspace: device scratch of at least tsp_csr_transpose_workspace(m, n, nnz) bytes,
  *   256-byte aligned; contents on entry are irrelevant.
  */
@@ -160,6 +172,45 @@ int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* valu
 /* values_t[r, p] = values[r, perm[p]] for a cached permutation (static topology). */
 int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int* perm,
                            float* values_t, void* stream);
+
+/*
+ * Per-topology plans ("optional transpose-plan cache"; the reference's
+ * topology is fixed at module construction, modules/sparse_attention.py:49-52,
+ * modules/sparse_linear.py:78-83, and its binding redoes the topology work on every call,
+ * src/transpose_cuda.cu:10-43).
+ *
+ * tsp_plan_create(m, n, nnz, row_offsets, column_indices, stream, &plan): a handle for the m x n
+ *   CSR topology.  row_offsets / column_indices are BORROWED device arrays that must stay valid and
+ *   unchanged for the plan's lifetime.  Launches the one sortedness check on `stream`; the verdict
+ *   reaches the host asynchronously (no synchronisation here), after which planned calls launch
+ *   exactly one kernel.  The plan also owns, built on first use: the block-start / occupancy-bitmap
+ *   views of the staged SDDMM kernels and the transposed topology + permutation.
+ *   Thread-safe: concurrent planned calls on one plan are allowed (internal mutex around view
+ *   creation); tsp_plan_destroy must not race with them.  The first use of a view allocates
+ *   (cudaMalloc): do it once before capturing a CUDA graph (a missing view during capture makes the
+ *   call take the view-free gather kernel instead).
+ * tsp_plan_sorted: 1 columns ascending in every row, 0 not, -1 verdict not on the host yet.
+ * tsp_plan_transpose: the plan of the TRANSPOSED topology (owned by `plan`, destroyed with it) and its
+ *   arrays: row_offsets_t[n+1], column_indices_t[nnz], perm[nnz] with values_t[p] = values[perm[p]],
+ *   bit-identical to tsp_csr_transpose_f32 / cusparseCsr2cscEx2(ALG1).  Any out pointer may be NULL.
+ *   A^T @ B without materialising values_t: tsp_plan_spmm_f32(transposed, ..., values, perm, ...).
+ * tsp_plan_spmm_f32 / tsp_plan_sddmm_f32: tsp_spmm_perm_f32 / tsp_sddmm_f32 (reduce == 0) /
+ *   tsp_sddmm_reduce_f32 (reduce != 0) on the plan's topology; m, k (resp. m, n) and nnz come from the
+ *   plan, `n` is the dense operand's column count (resp. `k` the inner dimension).
+ */
+typedef struct tsp_plan tsp_plan;
+int tsp_plan_create(int m, int n, int nnz, const int* row_offsets, const int* column_indices,
+                    void* stream, tsp_plan** plan_out);
+void tsp_plan_destroy(tsp_plan* plan);
+int tsp_plan_sorted(tsp_plan* plan);
+int tsp_plan_transpose(tsp_plan* plan, void* stream, tsp_plan** transposed_out,
+                       const int** row_offsets_t, const int** column_indices_t, const int** perm);
+int tsp_plan_spmm_f32(tsp_plan* plan, int n, int replicas, int values_shared,
+                      const int* row_indices, const float* values, const int* value_perm_or_null,
+                      const float* dense, const float* bias_or_null, int relu, float* out,
+                      void* stream);
+int tsp_plan_sddmm_f32(tsp_plan* plan, int k, int replicas, int reduce, const int* row_indices,
+                       const float* lhs, const float* rhs, float* out, void* stream);
 
 /*
  * Knobs for A/B benchmarking only (not part of the reference surface):

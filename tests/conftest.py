@@ -8,6 +8,11 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+# the staged copy of the reference's callers (see __graft_entry__.stage_reference_callers) is test
+# INPUT: it is imported by tests/test_gpu_ref_callers.py, never collected
+collect_ignore = ["_ref_callers"]
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

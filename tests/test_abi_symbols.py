@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     assert not missing, f"libtsp.so lacks {missing}"
     assert set(cabi.SYMBOLS) == set(_declared())
     lib.tsp_version.restype = ctypes.c_int
-    assert lib.tsp_version() == 1
+    assert lib.tsp_version() == 2
 
 
 def test_argument_errors_do_not_need_a_gpu():
@@ -37,6 +37,12 @@ def test_argument_errors_do_not_need_a_gpu():
     rc = lib.tsp_sddmm_f32(4, 4, 4, 4, 70000, None, None, None, None, None, None, None)
     assert rc == 1 and "65535" in cabi.last_error()
     assert lib.tsp_csr_transpose_workspace(4096, 4096, 1 << 20) >= 4 * 4 * (1 << 20)
+    plan = ctypes.c_void_p()
+    rc = lib.tsp_plan_create(-1, 4, 0, None, None, None, ctypes.byref(plan))
+    assert rc == 1 and plan.value is None and "negative" in cabi.last_error()
+    assert lib.tsp_plan_spmm_f32(None, 4, 1, 0, None, None, None, None, None, 0, None, None) == 1
+    assert lib.tsp_plan_sorted(None) == -1
+    lib.tsp_plan_destroy(None)
 
 
 def test_torch_module_surface(ops):

@@ -43,6 +43,30 @@ def test_spmm_function_grads(dev, replicas):
     torch.testing.assert_close(vals.grad.double(), vals64.grad, rtol=1e-5, atol=1e-5)
 
 
+def test_spmm_function_single_replica_with_2d_values(dev):
+    """values [1, nnz] x dense [1, k, n]: the forward returns 2-D (src/spmm_cuda.cu:46) and sddmm returns
+    [nnz] (src/sddmm_cuda.cu:43); the backward must still hand autograd a [1, nnz] gradient."""
+    from torch_sputnik_b200.modules import Spmm
+    m, k, n = 64, 48, 40
+    a = random_csr(m, k, 0.25, seed=31, values="pm1")
+    v, ri, ro, ci = to_dev(a, dev)
+    vals = torch.from_numpy(dense_operand((1, a.nnz), 32, "pm1")).to(dev).requires_grad_(True)
+    dense = torch.from_numpy(dense_operand((1, k, n), 33, "pm1")).to(dev).requires_grad_(True)
+    out = Spmm.apply(m, k, vals, ri, ro, ci, dense)
+    assert tuple(out.shape) == (m, n)
+    g = torch.from_numpy(dense_operand((m, n), 34, "pm1")).to(dev)
+    out.backward(g)
+    assert vals.grad.shape == vals.shape and dense.grad.shape == dense.shape
+    vals64 = vals.detach().double().requires_grad_(True)
+    dense64 = dense.detach().double().requires_grad_(True)
+    A, r, c = _dense_from(a, vals64, dev)
+    ref = (A @ dense64)[0]
+    ref.backward(g.double())
+    torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(vals.grad.double(), vals64.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(dense.grad.double(), dense64.grad, rtol=1e-5, atol=1e-5)
+
+
 @pytest.mark.parametrize("replicas", [0, 3])
 def test_sddmm_function_grads(dev, replicas):
     from torch_sputnik_b200.modules import Sddmm

@@ -55,6 +55,11 @@ spmm_many_mask = torch_sputnik.spmm_many_mask
 sddmm_many_mask = torch_sputnik.sddmm_many_mask
 sparse_softmax_many_mask = torch_sputnik.sparse_softmax_many_mask
 csr_transpose_many_mask = torch_sputnik.csr_transpose_many_mask
+sparse_softmax_many_mask_scaled = torch_sputnik.sparse_softmax_many_mask_scaled
+transposed_topology = torch_sputnik.transposed_topology
+plan_policy = torch_sputnik.plan_policy
+plan_cache_clear = torch_sputnik.plan_cache_clear
+plan_cache_stats = torch_sputnik.plan_cache_stats
 set_variant = torch_sputnik.set_variant
 launch_count = torch_sputnik.launch_count
 
@@ -62,5 +67,6 @@ __all__ = [
     "torch_sputnik", "spmm", "left_spmm", "sddmm", "sparse_softmax", "csr_transpose",
     "spmm_bias_relu", "spmm_bias", "sddmm_reduce", "sparse_softmax_scaled", "sparse_softmax_backward",
     "csr_transpose_with_perm", "permute_values", "sparse_attention", "spmm_perm", "spmm_many_mask", "sddmm_many_mask",
-    "sparse_softmax_many_mask", "csr_transpose_many_mask", "set_variant", "launch_count",
+    "sparse_softmax_many_mask", "csr_transpose_many_mask", "sparse_softmax_many_mask_scaled", "transposed_topology",
+    "plan_policy", "plan_cache_clear", "plan_cache_stats", "set_variant", "launch_count",
 ]

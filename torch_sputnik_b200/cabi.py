@@ -14,6 +14,8 @@ SYMBOLS = (
     "tsp_csr_softmax_backward_f32", "tsp_csr_transpose_workspace", "tsp_csr_transpose_f32",
     "tsp_permute_values_f32", "tsp_sparse_attention_supported", "tsp_sparse_attention_f32", "tsp_set_variant",
     "tsp_launch_count",
+    "tsp_plan_create", "tsp_plan_destroy", "tsp_plan_sorted", "tsp_plan_transpose", "tsp_plan_spmm_f32",
+    "tsp_plan_sddmm_f32",
 )
 
 _lib = None
@@ -42,6 +44,14 @@ def load() -> ctypes.CDLL:
         lib.tsp_sparse_attention_f32.argtypes = [i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_set_variant.argtypes = [ctypes.c_char_p, i]
         lib.tsp_launch_count.restype = ctypes.c_ulonglong
+        pp = ctypes.POINTER(vp)
+        lib.tsp_plan_create.argtypes = [i, i, i, vp, vp, vp, pp]
+        lib.tsp_plan_destroy.argtypes = [vp]
+        lib.tsp_plan_destroy.restype = None
+        lib.tsp_plan_sorted.argtypes = [vp]
+        lib.tsp_plan_transpose.argtypes = [vp, vp, pp, pp, pp, pp]
+        lib.tsp_plan_spmm_f32.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp, i, vp, vp]
+        lib.tsp_plan_sddmm_f32.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp]
         _lib = lib
     return _lib
 

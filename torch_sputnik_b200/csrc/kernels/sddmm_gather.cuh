@@ -13,7 +13,7 @@
 // Arithmetic matches sputnik::CudaSddmmKernel (cuda_sddmm.cu.cc:34-165): fp32 FMA along k per
 // lane, then fp32 tree sum across lanes.
 #pragma once
-#include "spmm_gather.cuh"  // g_unsorted_flag
+#include "spmm_gather.cuh"  // StagedGuard
 
 namespace tsp {
 
@@ -24,10 +24,9 @@ struct SddmmArgs {
   const float* lhs;  // [replicas, m, k]
   const float* rhs;  // [replicas, n, k]
   float* out;        // [replicas, nnz]
-  // guard_id != 0: this launch is the unsorted-columns fallback of a tiled launch and runs only
-  // if g_unsorted_flag[guard_slot] == guard_id.
-  int guard_slot = 0;
-  unsigned guard_id = 0;
+  // guard_flag != null: this launch is the unsorted-columns fallback of a staged launch and runs
+  // only if *guard_flag != 0 (see StagedGuard, spmm_gather.cuh).
+  const unsigned* guard_flag = nullptr;
   // reduce_reps > 0: out is ONE [nnz] vector holding the sum over that many replicas (the
   // weight gradient of a sparse linear layer); the staged kernels fold the replica loop into
   // their k loop, grid.y is 1.
@@ -66,7 +65,7 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   constexpr int NPG = LPN;     // nonzeros per group per chunk (G * NPG == 32)
   constexpr int KSTEP = LPN * VEC;
 
-  if (a.guard_id != 0 && g_unsorted_flag[a.guard_slot] != a.guard_id) return;
+  if (fallback_not_needed(a.guard_flag)) return;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int chunk = blockIdx.x * WARPS + warp;
@@ -139,12 +138,9 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   if (j < a.nnz) a.out[(size_t)rep * a.nnz + j] = acc[0];
 }
 
-// out[j] = sum_r scratch[r, j] (ascending r).  guard_id != 0: runs only as the unsorted-columns
-// fallback of a staged reduce launch (the staged kernel has written out[] itself otherwise).
+// out[j] = sum_r scratch[r, j] (ascending r).
 __global__ void __launch_bounds__(256)
-reduce_replicas_kernel(const float* __restrict__ scratch, int nnz, int replicas, float* __restrict__ out,
-                       int guard_slot, unsigned guard_id) {
-  if (guard_id != 0 && g_unsorted_flag[guard_slot] != guard_id) return;
+reduce_replicas_kernel(const float* __restrict__ scratch, int nnz, int replicas, float* __restrict__ out) {
   const int j = blockIdx.x * 256 + threadIdx.x;
   if (j >= nnz) return;
   float s = 0.f;

@@ -48,8 +48,8 @@ struct SddmmSampledCfg {
 // of launches per call, not by the work in them).
 __global__ void __launch_bounds__(256)
 csr_prepare_sampled_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m, int nb, int bn,
-                           int* __restrict__ starts, int check_blocks, int slot, unsigned call_id) {
-  if ((int)blockIdx.x < check_blocks) {
+                           int* __restrict__ starts, int check_blocks, unsigned* __restrict__ flag) {
+  if ((int)blockIdx.x < check_blocks) {   // (check_blocks == 0: the plan already ran the check)
     const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const int nwarps = (check_blocks * 256) >> 5;
     bool bad = false;
@@ -57,7 +57,7 @@ csr_prepare_sampled_kernel(const int* __restrict__ row_offsets, const int* __res
       const int beg = __ldg(row_offsets + row), end = __ldg(row_offsets + row + 1);
       for (int j = beg + lane; j + 1 < end; j += 32) bad |= __ldg(cols + j) >= __ldg(cols + j + 1);
     }
-    if (__any_sync(kFullMask, bad) && lane == 0) g_unsorted_flag[slot] = call_id;
+    if (__any_sync(kFullMask, bad) && lane == 0) *flag = 1u;
     return;
   }
   const long long t = (long long)(blockIdx.x - check_blocks) * 256 + threadIdx.x;
@@ -94,7 +94,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
                      const int* __restrict__ starts, const __grid_constant__ CUtensorMap tm_lhs,
                      const __grid_constant__ CUtensorMap tm_rhs, const int ksplit) {
   constexpr int BM = Cfg::BM, BK = Cfg::BK, P = Cfg::P, STAGES = Cfg::STAGES, CAP = Cfg::CAP;
-  if (g_unsorted_flag[guard.slot] == guard.call_id) return;
+  if (staged_declines(guard)) return;
 
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* const smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
@@ -302,9 +302,23 @@ inline int sddmm_sampled_ksplit(long long tiles, int grid_reps, int ksteps_all) 
   return (int)std::max<long long>(1, std::min<long long>(ks, 64));
 }
 
+// Block-start view of an m-row mask for tile width bn: (ceil(n / bn) + 1) ints per row.
+inline size_t sddmm_sampled_view_bytes(int m, int n, int bn) { return (size_t)m * (ceil_div(n, bn) + 1) * 4 + 256; }
+
+// Builds the view into `ws`; flag_or_null != null also runs the sortedness check in the same launch.
+inline int build_sddmm_sampled_view(const int* row_offsets, const int* column_indices, int m, int n, int bn,
+                                    void* ws, unsigned* flag_or_null, cudaStream_t stream) {
+  const int nb = ceil_div(n, bn);
+  const int check_blocks = flag_or_null ? min(ceil_div(m, 8), 4 * sm_count()) : 0;
+  csr_prepare_sampled_kernel<<<check_blocks + (int)ceil_div((long long)m * (nb + 1), 256), 256, 0, stream>>>(
+      row_offsets, column_indices, m, nb, bn, static_cast<int*>(ws), check_blocks, flag_or_null);
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (block starts)");
+  return 0;
+}
+
 template <class Cfg, int NB_LO>
 inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_t stream,
-                                   const StagedGuard& guard, int bn) {
+                                   const StagedGuard& guard, int bn, const int* starts) {
   const int row_blocks = ceil_div(a.m, Cfg::BM), nb = ceil_div(a.n, bn);
   const size_t smem = Cfg::smem_bytes(bn);
   static bool configured[64] = {false};
@@ -316,18 +330,9 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
     if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled smem attribute)");
     configured[dev] = true;
   }
-  void* ws = nullptr;
-  cudaError_t e = cudaMallocAsync(&ws, (size_t)a.m * (nb + 1) * 4 + 256, stream);
-  if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled scratch)");
-  int* starts = static_cast<int*>(ws);
-  const int check_blocks = min(ceil_div(a.m, 8), 4 * sm_count());
-  csr_prepare_sampled_kernel<<<check_blocks + (int)ceil_div((long long)a.m * (nb + 1), 256), 256, 0, stream>>>(
-      a.row_offsets, a.column_indices, a.m, nb, bn, starts, check_blocks, guard.slot, guard.call_id);
-  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sorted check + block starts)");
   CUtensorMap tm_lhs, tm_rhs;
   if (!encode_rowmajor_map_plain(&tm_lhs, a.lhs, replicas, a.m, a.k, Cfg::BM) ||
       !encode_rowmajor_map_plain(&tm_rhs, a.rhs, replicas, a.n, a.k, bn)) {
-    cudaFreeAsync(ws, stream);
     set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
     return 2;
   }
@@ -340,11 +345,8 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
   SddmmArgs b = a;
   float* partial = nullptr;
   if (ksplit > 1) {
-    e = cudaMallocAsync(reinterpret_cast<void**>(&partial), sizeof(float) * (size_t)ksplit * a.nnz, stream);
-    if (e != cudaSuccess) {
-      cudaFreeAsync(ws, stream);
-      return cuda_fail(e, "tsp_sddmm_f32 (split-K scratch)");
-    }
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&partial), sizeof(float) * (size_t)ksplit * a.nnz, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (split-K scratch)");
     b.out = partial;
   }
   dim3 grid(row_blocks * nb, grid_reps, ksplit);
@@ -353,26 +355,25 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
   if (ksplit > 1) {
     // (with unsorted columns the sampled kernel exits and this sums garbage; the guarded gather
     // fallback queued behind by the caller then rewrites every element of out)
-    reduce_replicas_kernel<<<ceil_div(a.nnz, 256), 256, 0, stream>>>(partial, a.nnz, ksplit, a.out, 0, 0u);
+    reduce_replicas_kernel<<<ceil_div(a.nnz, 256), 256, 0, stream>>>(partial, a.nnz, ksplit, a.out);
     TSP_CHECK_LAUNCH("tsp_sddmm_f32 (split-K sum)");
     cudaFreeAsync(partial, stream);
   }
-  cudaFreeAsync(ws, stream);
   return 0;
 }
 
 template <class Cfg>
 inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream_t stream,
-                                    const StagedGuard& guard, int bn) {
+                                    const StagedGuard& guard, int bn, const int* starts) {
   // Batches every tile is expected to fill: (mu - 4 sigma) / 32 slots per group, 4 slots per batch.
   const double density = (double)a.nnz / ((double)a.m * (double)a.n);
   const double mu = (double)Cfg::BM * bn * density;
   const double lo = mu - 4.0 * sqrt(mu);
   const int nb_lo = lo > 0 ? (int)(lo / Cfg::GROUPS) / 4 : 0;
-  if (nb_lo >= 12 && Cfg::P >= 48) return launch_sddmm_sampled_nb<Cfg, 12>(a, replicas, stream, guard, bn);
-  if (nb_lo >= 8) return launch_sddmm_sampled_nb<Cfg, 8>(a, replicas, stream, guard, bn);
-  if (nb_lo >= 4) return launch_sddmm_sampled_nb<Cfg, 4>(a, replicas, stream, guard, bn);
-  return launch_sddmm_sampled_nb<Cfg, 0>(a, replicas, stream, guard, bn);
+  if (nb_lo >= 12 && Cfg::P >= 48) return launch_sddmm_sampled_nb<Cfg, 12>(a, replicas, stream, guard, bn, starts);
+  if (nb_lo >= 8) return launch_sddmm_sampled_nb<Cfg, 8>(a, replicas, stream, guard, bn, starts);
+  if (nb_lo >= 4) return launch_sddmm_sampled_nb<Cfg, 4>(a, replicas, stream, guard, bn, starts);
+  return launch_sddmm_sampled_nb<Cfg, 0>(a, replicas, stream, guard, bn, starts);
 }
 
 // Tile width: among the multiples of 8 columns (<= 256, <= n) whose expected nonzero count plus
@@ -412,22 +413,19 @@ inline int sddmm_sampled_tile_width(const SddmmArgs& a, int replicas) {
   return best;
 }
 
-// Returns 0 / an error code.  The gather kernel is launched behind it as the unsorted fallback.
-inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t stream, StagedGuard* guard_out,
-                                int bn_override = 0, int p_override = 0) {
-  unsigned id = g_call_counter.fetch_add(1) + 1;
-  if (id == 0) id = g_call_counter.fetch_add(1) + 1;
-  StagedGuard guard{(int)(id % kFlagSlots), id};
-  *guard_out = guard;
+// Tile width the launcher below wants for this call (the key of the block-start view in the plan).
+inline int sddmm_sampled_pick_bn(const SddmmArgs& a, int replicas, int bn_override = 0, int p_override = 0) {
+  if (bn_override > 0) return bn_override;
   const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;   // tiles are spread over this many grid.y slices
-  if (p_override == 48) {
-    using Cfg = SddmmSampledCfg<48, 2>;
-    const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, grid_reps);
-    return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
-  }
-  using Cfg = SddmmSampledCfg<56, 2>;
-  const int bn = bn_override > 0 ? bn_override : sddmm_sampled_tile_width<Cfg>(a, grid_reps);
-  return launch_sddmm_sampled_cfg<Cfg>(a, replicas, stream, guard, bn);
+  if (p_override == 48) return sddmm_sampled_tile_width<SddmmSampledCfg<48, 2>>(a, grid_reps);
+  return sddmm_sampled_tile_width<SddmmSampledCfg<56, 2>>(a, grid_reps);
+}
+
+// Returns 0 / an error code.  `starts` is the block-start view for width bn (from the plan).
+inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t stream, const StagedGuard& guard,
+                                int bn, const int* starts, int p_override = 0) {
+  if (p_override == 48) return launch_sddmm_sampled_cfg<SddmmSampledCfg<48, 2>>(a, replicas, stream, guard, bn, starts);
+  return launch_sddmm_sampled_cfg<SddmmSampledCfg<56, 2>>(a, replicas, stream, guard, bn, starts);
 }
 
 }  // namespace tsp

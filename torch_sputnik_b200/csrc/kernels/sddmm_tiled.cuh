@@ -46,7 +46,7 @@ struct SddmmTiled {
 __global__ void __launch_bounds__(256)
 csr_block_masks_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m,
                        int col_blocks, unsigned long long* __restrict__ masks, int* __restrict__ bases,
-                       int slot, unsigned call_id) {
+                       unsigned* __restrict__ flag) {
   const int row = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (row >= m) return;
   const int beg = __ldg(row_offsets + row), end = __ldg(row_offsets + row + 1);
@@ -73,7 +73,7 @@ csr_block_masks_kernel(const int* __restrict__ row_offsets, const int* __restric
       active &= ~__ballot_sync(kFullMask, sel);
     }
   }
-  if (__any_sync(kFullMask, bad) && lane == 0) g_unsorted_flag[slot] = call_id;
+  if (flag != nullptr && __any_sync(kFullMask, bad) && lane == 0) *flag = 1u;
 }
 
 __global__ void __launch_bounds__(SddmmTiled::THREADS, 2)
@@ -83,7 +83,7 @@ sddmm_tiled_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_cta
                    const __grid_constant__ CUtensorMap tm_rhs) {
   using C = SddmmTiled;
   constexpr int BM = C::BM, BN = C::BN, BK = C::BK, STAGES = C::STAGES;
-  if (g_unsorted_flag[guard.slot] == guard.call_id) return;
+  if (staged_declines(guard)) return;
 
   extern __shared__ unsigned char smem_dyn[];
   // swizzle-128B tiles want 1024-byte aligned destinations
@@ -240,7 +240,7 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
                     const __grid_constant__ CUtensorMap tm_rhs) {
   using C = SddmmTiled2;
   constexpr int BM = C::BM, BN = C::BN, BK = C::BK, STAGES = C::STAGES;
-  if (g_unsorted_flag[guard.slot] == guard.call_id) return;
+  if (staged_declines(guard)) return;
 
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* const smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
@@ -417,14 +417,28 @@ inline bool sddmm_tiled_applicable(const SddmmArgs& a, int replicas) {
   return 2.0 * a.nnz * a.k * replicas >= 5.0e7;
 }
 
-// Returns 0 / an error code.  The gather kernel is launched behind it as the unsorted fallback.
-inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t stream, StagedGuard* guard_out,
-                             bool v1 = false) {
+// Bytes of the bitmap view of an m-row mask with `col_blocks` 64-column blocks: a 64-bit occupancy
+// word + the flat index of the first nonzero per (row, block).
+inline size_t sddmm_tiled_view_bytes(int m, int col_blocks) { return (size_t)m * col_blocks * 12 + 256; }
+
+// Builds the bitmap view into `ws` (sddmm_tiled_view_bytes); flag_or_null != null also runs the
+// sortedness check in the same pass.
+inline int build_sddmm_tiled_view(const int* row_offsets, const int* column_indices, int m, int col_blocks,
+                                  void* ws, unsigned* flag_or_null, cudaStream_t stream) {
+  const size_t entries = (size_t)m * col_blocks;
+  unsigned long long* masks = static_cast<unsigned long long*>(ws);
+  int* bases = reinterpret_cast<int*>(masks + entries);
+  cudaMemsetAsync(masks, 0, entries * 8, stream);
+  csr_block_masks_kernel<<<ceil_div((long long)m * 32, 256), 256, 0, stream>>>(
+      row_offsets, column_indices, m, col_blocks, masks, bases, flag_or_null);
+  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (block masks)");
+  return 0;
+}
+
+// Returns 0 / an error code.  `view` is the bitmap view of the topology (from its plan).
+inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t stream, const StagedGuard& guard,
+                              const void* view, bool v1 = false) {
   using C = SddmmTiled;
-  unsigned id = g_call_counter.fetch_add(1) + 1;
-  if (id == 0) id = g_call_counter.fetch_add(1) + 1;
-  StagedGuard guard{(int)(id % kFlagSlots), id};
-  *guard_out = guard;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -445,21 +459,12 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
   int per_cta = (int)((total * grid_reps + slots - 1) / slots);
   per_cta = per_cta < 1 ? 1 : (per_cta > col_blocks ? col_blocks : per_cta);
   const int ctas = (int)((total + per_cta - 1) / per_cta);
-  // Stream-ordered scratch for the bitmap view (12 bytes per (row, 64-column block)).
   const size_t entries = (size_t)a.m * col_blocks;
-  void* ws = nullptr;
-  cudaError_t e = cudaMallocAsync(&ws, entries * 12 + 256, stream);
-  if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (tiled scratch)");
-  unsigned long long* masks = static_cast<unsigned long long*>(ws);
-  int* bases = reinterpret_cast<int*>(masks + entries);
-  cudaMemsetAsync(masks, 0, entries * 8, stream);
-  csr_block_masks_kernel<<<ceil_div((long long)a.m * 32, 256), 256, 0, stream>>>(
-      a.row_offsets, a.column_indices, a.m, col_blocks, masks, bases, guard.slot, guard.call_id);
-  TSP_CHECK_LAUNCH("tsp_sddmm_f32 (block masks)");
+  const unsigned long long* masks = static_cast<const unsigned long long*>(view);
+  const int* bases = reinterpret_cast<const int*>(masks + entries);
   CUtensorMap tm_lhs, tm_rhs;
   if (!encode_rowmajor_map(&tm_lhs, a.lhs, replicas, a.m, a.k, C::BM) ||
       !encode_rowmajor_map(&tm_rhs, a.rhs, replicas, a.n, a.k, C::BN)) {
-    cudaFreeAsync(ws, stream);
     set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
     return 2;
   }
@@ -471,7 +476,6 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
     sddmm_tiled2_kernel<<<grid, SddmmTiled2::THREADS, SddmmTiled2::kSmemBytes, stream>>>(
         a, guard, per_cta, col_blocks, (int)total, masks, bases, tm_lhs, tm_rhs);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (tiled)");
-  cudaFreeAsync(ws, stream);
   return 0;
 }
 

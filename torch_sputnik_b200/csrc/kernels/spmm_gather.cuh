@@ -32,15 +32,23 @@ struct SpmmArgs {
   // TRANSPOSE of the matrix the values are stored for (perm from tsp_csr_transpose_f32), so a
   // backward pass multiplies by A^T without materialising the permuted [replicas, nnz] values.
   const int* value_perm = nullptr;
-  // When guard_id != 0 the gather kernel is the fallback of a staged launch: it runs only if the
-  // sorted-columns check raised g_unsorted_flag[guard_slot] == guard_id.
-  int guard_slot = 0;
-  unsigned guard_id = 0;
+  // guard_flag != null: this launch is the unsorted-columns fallback of a staged launch and runs
+  // only if the sorted-columns check raised *guard_flag (a device word owned by the call's plan).
+  const unsigned* guard_flag = nullptr;
 };
 
-// Per-call "columns are not sorted" flags, written by csr_check_sorted_kernel (spmm_staged.cuh).
-constexpr int kFlagSlots = 1024;
-__device__ unsigned g_unsorted_flag[kFlagSlots];
+// "Columns are not sorted" verdict of ONE topology: a device word owned by the topology's plan
+// (plan.cuh) -- persistent for a planned topology, stream-ordered scratch for an unplanned call.
+// flag == null: the host already knows the columns are sorted; no device check, no fallback.
+struct StagedGuard {
+  const unsigned* flag;
+};
+__device__ __forceinline__ bool staged_declines(const StagedGuard& g) {
+  return g.flag != nullptr && *reinterpret_cast<const volatile unsigned*>(g.flag) != 0u;
+}
+__device__ __forceinline__ bool fallback_not_needed(const unsigned* guard_flag) {
+  return guard_flag != nullptr && *reinterpret_cast<const volatile unsigned*>(guard_flag) == 0u;
+}
 
 template <int VEC>
 struct VecT;
@@ -89,7 +97,7 @@ __device__ __forceinline__ void store_vec(float* p, const float (&src)[VEC]) {
 template <int VEC, int U, int WARPS, bool OFF32>
 __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs a) {
   __shared__ __align__(16) int2 s_pairs[WARPS][32];
-  if (a.guard_id != 0 && g_unsorted_flag[a.guard_slot] != a.guard_id) return;
+  if (fallback_not_needed(a.guard_flag)) return;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;

@@ -20,7 +20,11 @@
 //    arithmetic and rounding, leaving issue room for the LDS and the bit-walk.
 //
 // Arithmetic: per output element, fp32 FMAs in ascending column order, exactly the reference's
-// order; entries a row does not have contribute fma(0, b, acc) = acc for finite b.
+// order; entries a row does not have contribute fma(0, b, acc) = acc for finite b.  A non-finite b
+// would leak into the rows merged with the one that owns the column (0 * Inf = NaN), which the
+// reference never does (cuda_spmm.cu.cc:224-238 reads only the dense rows a row names): the epilogue
+// therefore tests every row's accumulators and recomputes a row that holds a non-finite value
+// the way the gather kernel does, from its own nonzeros only (spmm_staged_redo_row).
 // Precondition: column indices strictly ascending inside each row (what to_sparse_csr and the
 // reference's generators produce).  tsp_spmm_f32 verifies it on the device in the same stream
 // (csr_check_sorted_kernel) and falls back to the gather kernel if it does not hold.
@@ -29,10 +33,10 @@
 
 namespace tsp {
 
-// flag[slot] = call_id if some row has a column index not greater than its predecessor.
+// *flag = 1 if some row has a column index not greater than its predecessor (*flag is 0 on entry).
 __global__ void __launch_bounds__(256)
 csr_check_sorted_kernel(const int* __restrict__ row_offsets, const int* __restrict__ cols, int m,
-                        int slot, unsigned call_id) {
+                        unsigned* __restrict__ flag) {
   const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   const int nwarps = (gridDim.x * 256) >> 5;
   bool bad = false;
@@ -40,7 +44,7 @@ csr_check_sorted_kernel(const int* __restrict__ row_offsets, const int* __restri
     const int beg = __ldg(row_offsets + row), end = __ldg(row_offsets + row + 1);
     for (int j = beg + lane; j + 1 < end; j += 32) bad |= __ldg(cols + j) >= __ldg(cols + j + 1);
   }
-  if (__any_sync(kFullMask, bad) && lane == 0) g_unsorted_flag[slot] = call_id;
+  if (__any_sync(kFullMask, bad) && lane == 0) *flag = 1u;
 }
 
 __device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
@@ -76,17 +80,46 @@ struct StagedCfg {
       sizeof(float) * (STAGES_ * kSlabFloats + (size_t)WARPS_ * G_ * kTileFloats) + 2 * STAGES_ * 8 + 128;
 };
 
-struct StagedGuard {
-  int slot;          // index into g_unsorted_flag
-  unsigned call_id;  // this call's id; flag == call_id  <=>  columns are not sorted
-};
+// Rare path of the staged epilogue: one output row x this lane's NV4 float4 columns, recomputed in
+// CSR order from the row's own nonzeros (global-memory gathers), bias / ReLU applied, stored.
+template <int NV4>
+__device__ __noinline__ void spmm_staged_redo_row(const float* __restrict__ dense, const float* __restrict__ vals,
+                                                  const int* __restrict__ cols, int beg, int end, int n, int n0,
+                                                  int lane, float bias, int relu, float* __restrict__ out) {
+  float4 acc[NV4];
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int p = beg; p < end; ++p) {
+    const float v = __ldg(vals + p);
+    const float* brow = dense + (size_t)__ldg(cols + p) * n + n0 + lane * 4;
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+      if (n0 + lane * 4 + j * 128 >= n) continue;
+      const float4 b = __ldg(reinterpret_cast<const float4*>(brow + j * 128));
+      acc[j].x = fmaf(v, b.x, acc[j].x);
+      acc[j].y = fmaf(v, b.y, acc[j].y);
+      acc[j].z = fmaf(v, b.z, acc[j].z);
+      acc[j].w = fmaf(v, b.w, acc[j].w);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NV4; ++j) {
+    if (n0 + lane * 4 + j * 128 >= n) continue;
+    float4 o = acc[j];
+    o.x += bias; o.y += bias; o.z += bias; o.w += bias;
+    if (relu) {
+      o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+    }
+    *reinterpret_cast<float4*>(out + j * 128) = o;
+  }
+}
 
 template <class Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS, (Cfg::kSmemBytes <= 110 * 1024) ? 2 : 1)
 spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   constexpr int NV4 = Cfg::NV4, NT = Cfg::NT, G = Cfg::G, KS = Cfg::KS, STAGES = Cfg::STAGES,
                 WARPS = Cfg::WARPS, U = Cfg::U, R = Cfg::R, LPR = Cfg::LPR;
-  if (g_unsorted_flag[guard.slot] == guard.call_id) return;  // gather kernel takes over
+  if (staged_declines(guard)) return;  // gather kernel takes over
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* const b_ring = reinterpret_cast<float*>(smem_raw);
@@ -303,8 +336,22 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
       const int item = blockIdx.x * Cfg::RB + (warp * G + g) * R + r;
       if (item >= a.m) continue;
       const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
+      // x - x is 0 for finite x and NaN otherwise; one sum per row finds any non-finite accumulator
+      // (an Inf born of finite operands also lands here: the redo then reproduces it).
+      float probe = 0.f;
+#pragma unroll
+      for (int j = 0; j < NV4 * 2; ++j) {
+        float lo, hi;
+        unpack2(acc[g][r][j], lo, hi);
+        probe += (lo - lo) + (hi - hi);
+      }
       const float bias = a.bias ? __ldg(a.bias + row) : 0.f;
       float* __restrict__ out = a.out + ((size_t)rep * a.m + row) * n + n0 + lane * 4;
+      if (__any_sync(kFullMask, probe != 0.f)) {
+        spmm_staged_redo_row<NV4>(a.dense + (size_t)rep * k * n, vals, cols, __ldg(a.row_offsets + row),
+                                  __ldg(a.row_offsets + row + 1), n, n0, lane, bias, a.relu, out);
+        continue;
+      }
 #pragma unroll
       for (int j = 0; j < NV4; ++j) {
         if (n0 + lane * 4 + j * 128 >= n) continue;
@@ -348,20 +395,12 @@ inline int launch_spmm_staged_cfg(const SpmmArgs& a, int replicas, const StagedG
   return 0;
 }
 
-static std::atomic<unsigned> g_call_counter{0};
-
-// Returns TSP_OK / an error code, or -1 if the staged path declines (caller uses gather).
+// Returns TSP_OK / an error code.  The sortedness verdict comes from the topology's plan (plan.cuh):
+// guard.flag == null when the host already knows the columns are sorted, else the plan's device
+// word -- the caller then queues the guarded gather launch behind this one.
 // rows_per_group: 0 = pick from the density, 4 or 8 = forced (benchmark knob).
-inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stream,
+inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stream, const StagedGuard& guard,
                               int rows_per_group = 0) {
-  unsigned id = g_call_counter.fetch_add(1) + 1;
-  if (id == 0) id = g_call_counter.fetch_add(1) + 1;
-  StagedGuard guard{(int)(id % kFlagSlots), id};
-
-  csr_check_sorted_kernel<<<min(ceil_div(a.m, 8), 4 * sm_count()), 256, 0, stream>>>(
-      a.row_offsets, a.column_indices, a.m, guard.slot, guard.call_id);
-  TSP_CHECK_LAUNCH("tsp_spmm_f32 (sorted check)");
-
   // Candidates prefetched per row per slab = LPR*U; sized so that a row's count in a 32-column
   // slab (mean avg = 32*density) almost never exceeds it.
   const double density = (double)a.nnz / ((double)a.m * (double)a.k);
@@ -394,14 +433,6 @@ inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stre
   }
   if (rc != 0) return rc;
   TSP_CHECK_LAUNCH("tsp_spmm_f32 (staged)");
-
-  // Fallback for unsorted columns: same arguments through the gather kernel, which exits at once
-  // unless the check kernel raised this call's flag.
-  SpmmArgs f = a;
-  f.guard_slot = guard.slot;
-  f.guard_id = guard.call_id;
-  launch_spmm_gather<4, 2>(f, replicas, stream);
-  TSP_CHECK_LAUNCH("tsp_spmm_f32 (gather fallback)");
   return 0;
 }
 

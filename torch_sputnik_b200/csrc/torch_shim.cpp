@@ -11,10 +11,15 @@
 // include/tsp.h; there is no CPU or library fallback.
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
+#include <cuda_runtime_api.h>
 #include <torch/extension.h>
 
 #include <algorithm>
 #include <cstdint>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <tuple>
 #include <vector>
 
 #include "../../include/tsp.h"
@@ -37,6 +42,18 @@ void check_rc(int rc, const char* op) {
   TORCH_CHECK(rc == TSP_OK, "torch_sputnik.", op, " failed (", rc, "): ", tsp_last_error());
 }
 
+// A float32 CUDA operand, made contiguous.  The reference assumes contiguity and reads garbage
+// otherwise: its own callers hand the ops transposed views in backward (the gradient of
+// `.transpose(1,2).contiguous()` in modules/sparse_attention.py:108 reaches
+// SparseLinearFunction.backward, modules/sparse_linear.py:44,60, as a non-contiguous view), so the
+// shim copies instead of failing.
+torch::Tensor f32_operand(const torch::Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda(), "torch_sputnik: ", name, " must be a CUDA tensor");
+  TORCH_CHECK(t.scalar_type() == torch::kFloat32, "torch_sputnik: ", name, " must be float32, got ",
+              t.scalar_type());
+  return t.contiguous();
+}
+
 // modules/sparse_linear.py:5-7,57 hands an int64 row_indices to left_spmm in backward; the
 // reference's data_ptr<int>() would throw.  Accept it and narrow.
 torch::Tensor as_i32_indices(const torch::Tensor& t, const char* name) {
@@ -48,6 +65,15 @@ torch::Tensor as_i32_indices(const torch::Tensor& t, const char* name) {
 }
 
 void* current_stream() { return static_cast<void*>(at::cuda::getCurrentCUDAStream().stream()); }
+
+bool current_stream_capturing() {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(at::cuda::getCurrentCUDAStream().stream(), &st) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
 
 void check_topology(int64_t m, const torch::Tensor& row_indices, const torch::Tensor& row_offsets,
                     const torch::Tensor& column_indices) {
@@ -62,18 +88,161 @@ void check_topology(int64_t m, const torch::Tensor& row_indices, const torch::Te
   TSP_CHECK_CUDA_I32(column_indices, "column_indices");
 }
 
+// ------------------------------------------------------------------------------- plan cache
+// One tsp_plan per topology the process has seen ("optional transpose-plan cache
+// ... mutex-guarded and keyed on (data_ptr, numel, _version)").  The reference's callers keep their
+// topology tensors for the life of the module (modules/sparse_attention.py:49-52,
+// modules/sparse_linear.py:78-83) and pass them to every call, so the plan is found by address.
+// An entry HOLDS the two index tensors: their storage cannot be freed -- and its address handed
+// to a different topology by the caching allocator -- while the entry lives, and an in-place edit
+// bumps _version, which is compared on every hit.  LRU-bounded.
+struct PlanHolder {
+  tsp_plan* plan = nullptr;
+  ~PlanHolder() { tsp_plan_destroy(plan); }
+};
+
+struct PlanEntry {
+  std::shared_ptr<PlanHolder> holder;   // owner of `plan` (the PARENT's holder for a transposed child)
+  tsp_plan* plan = nullptr;
+  torch::Tensor row_offsets, column_indices;   // keep the storage (and so the address) alive
+  uint32_t ro_version = 0, ci_version = 0;
+  // transposed topology, filled on demand: views of the plan's own device arrays
+  torch::Tensor ro_t, ci_t, perm, ri_t;
+  int64_t nnz = 0;
+  uint64_t tick = 0;
+};
+
+using PlanKey = std::tuple<const void*, const void*, int64_t, int64_t, int64_t>;
+
+struct PlanCache {
+  std::mutex mu;
+  std::map<PlanKey, std::shared_ptr<PlanEntry>> entries;
+  uint64_t tick = 0, hits = 0, misses = 0, evictions = 0;
+  int policy = 1;        // 0: never plan (every call takes the unplanned C-ABI entry), 1: plan on first sight
+  size_t capacity = 256;
+};
+
+PlanCache& plan_cache() {
+  static PlanCache* c = new PlanCache();   // never destroyed: no CUDA calls during interpreter teardown
+  return *c;
+}
+
+void evict_locked(PlanCache& c) {
+  while (c.entries.size() > c.capacity) {
+    auto victim = c.entries.begin();
+    for (auto it = c.entries.begin(); it != c.entries.end(); ++it)
+      if (it->second->tick < victim->second->tick) victim = it;
+    c.entries.erase(victim);
+    ++c.evictions;
+  }
+}
+
+// The plan of the m x n topology at (ro_ptr, ci_ptr), slices of the two tensors; nullptr when
+// planning is off or a new plan cannot be made right now (stream under CUDA-graph capture).
+std::shared_ptr<PlanEntry> get_plan(int64_t m, int64_t n, int64_t nnz, const torch::Tensor& row_offsets,
+                                    const int* ro_ptr, const torch::Tensor& column_indices, const int* ci_ptr) {
+  PlanCache& c = plan_cache();
+  const PlanKey key{ro_ptr, ci_ptr, m, n, nnz};
+  std::lock_guard<std::mutex> lock(c.mu);
+  if (c.policy == 0) return nullptr;
+  auto it = c.entries.find(key);
+  if (it != c.entries.end()) {
+    PlanEntry& e = *it->second;
+    if (e.ro_version == row_offsets._version() && e.ci_version == column_indices._version() &&
+        e.row_offsets.data_ptr() == row_offsets.data_ptr() &&
+        e.column_indices.data_ptr() == column_indices.data_ptr()) {
+      e.tick = ++c.tick;
+      ++c.hits;
+      return it->second;
+    }
+    c.entries.erase(it);   // edited in place (or another view of the storage): plan again
+  }
+  ++c.misses;
+  if (current_stream_capturing()) return nullptr;
+  auto e = std::make_shared<PlanEntry>();
+  e->holder = std::make_shared<PlanHolder>();
+  check_rc(tsp_plan_create((int)m, (int)n, (int)nnz, ro_ptr, ci_ptr, current_stream(), &e->holder->plan),
+           "plan_create");
+  e->plan = e->holder->plan;
+  e->row_offsets = row_offsets;
+  e->column_indices = column_indices;
+  e->ro_version = row_offsets._version();
+  e->ci_version = column_indices._version();
+  e->nnz = nnz;
+  e->tick = ++c.tick;
+  c.entries[key] = e;
+  evict_locked(c);
+  return e;
+}
+
+std::shared_ptr<PlanEntry> get_plan(int64_t m, int64_t n, const torch::Tensor& row_offsets,
+                                    const torch::Tensor& column_indices) {
+  return get_plan(m, n, column_indices.size(0), row_offsets, row_offsets.data_ptr<int>(), column_indices,
+                  column_indices.data_ptr<int>());
+}
+
+// Row swizzle of a topology: heaviest row first (tests/sparse_matrix.py:22), int32.
+torch::Tensor heaviest_first(const torch::Tensor& row_offsets) {
+  const int64_t rows = row_offsets.size(0) - 1;
+  torch::Tensor lens = row_offsets.slice(0, 1, rows + 1) - row_offsets.slice(0, 0, rows);
+  return torch::argsort(lens, /*stable=*/true, /*dim=*/0, /*descending=*/true).to(torch::kInt32);
+}
+
+// Fills e.ro_t / e.ci_t / e.perm / e.ri_t (views of the plan's device arrays, kept alive by the
+// holder) and registers the child plan under the transposed arrays' addresses, so an
+// `spmm(k, m, values_t, row_indices_t, row_offsets_t, column_indices_t, ...)` that follows
+// (modules/spmm.py:67-73) finds it.
+void ensure_transposed(const std::shared_ptr<PlanEntry>& e, int64_t m, int64_t n, const torch::Device& device) {
+  PlanCache& c = plan_cache();
+  {
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (e->ro_t.defined()) {
+      TORCH_CHECK(e->ro_t._version() == 0 && e->ci_t._version() == 0 && e->perm._version() == 0,
+                  "torch_sputnik.csr_transpose: the transposed index tensors of this topology are shared between "
+                  "calls and were modified in place; clone() them before editing");
+      return;
+    }
+  }
+  tsp_plan* child = nullptr;
+  const int *ro_t = nullptr, *ci_t = nullptr, *perm = nullptr;
+  check_rc(tsp_plan_transpose(e->plan, current_stream(), &child, &ro_t, &ci_t, &perm), "plan_transpose");
+  auto iopt = torch::TensorOptions().dtype(torch::kInt32).device(device);
+  std::shared_ptr<PlanHolder> keep = e->holder;
+  auto deleter = [keep](void*) {};
+  const int64_t count = e->nnz;   // (a many-mask slice has fewer entries than the tensor it lives in)
+  torch::Tensor ro_t_t = torch::from_blob(const_cast<int*>(ro_t), {n + 1}, deleter, iopt);
+  torch::Tensor ci_t_t = torch::from_blob(const_cast<int*>(ci_t), {count}, deleter, iopt);
+  torch::Tensor perm_t = torch::from_blob(const_cast<int*>(perm), {count}, deleter, iopt);
+  torch::Tensor ri_t = heaviest_first(ro_t_t);
+  std::lock_guard<std::mutex> lock(c.mu);
+  if (e->ro_t.defined()) return;
+  e->ro_t = ro_t_t;
+  e->ci_t = ci_t_t;
+  e->perm = perm_t;
+  e->ri_t = ri_t;
+  auto ce = std::make_shared<PlanEntry>();
+  ce->holder = e->holder;
+  ce->plan = child;
+  ce->row_offsets = ro_t_t;
+  ce->column_indices = ci_t_t;
+  ce->nnz = count;
+  ce->tick = ++c.tick;
+  c.entries[PlanKey{ro_t, ci_t, n, m, count}] = ce;
+  evict_locked(c);
+}
+
 // Shared body of spmm / left_spmm / spmm_bias_relu.
-torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values,
+torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values_in,
                         const torch::Tensor& row_indices_in, const torch::Tensor& row_offsets,
-                        const torch::Tensor& column_indices, const torch::Tensor& dense,
+                        const torch::Tensor& column_indices, const torch::Tensor& dense_in,
                         const c10::optional<torch::Tensor>& bias, bool relu, bool left,
                         const char* op, const c10::optional<torch::Tensor>& value_perm = c10::nullopt) {
-  TORCH_CHECK(values.dim() == 1 || values.dim() == 2, "torch_sputnik.", op,
+  TORCH_CHECK(values_in.dim() == 1 || values_in.dim() == 2, "torch_sputnik.", op,
               ": values must have 1 or 2 dimensions");
-  TORCH_CHECK(dense.dim() == 2 || dense.dim() == 3, "torch_sputnik.", op,
+  TORCH_CHECK(dense_in.dim() == 2 || dense_in.dim() == 3, "torch_sputnik.", op,
               ": dense must have 2 or 3 dimensions");
-  TSP_CHECK_CUDA_F32(values, "values");
-  TSP_CHECK_CUDA_F32(dense, "dense");
+  torch::Tensor values = f32_operand(values_in, "values");
+  torch::Tensor dense = f32_operand(dense_in, "dense");
   c10::cuda::CUDAGuard guard(values.device());
   torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
   check_topology(m, row_indices, row_offsets, column_indices);
@@ -95,8 +264,7 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values,
   const float* bias_ptr = nullptr;
   torch::Tensor bias_t;
   if (bias.has_value()) {
-    bias_t = *bias;
-    TSP_CHECK_CUDA_F32(bias_t, "bias");
+    bias_t = f32_operand(*bias, "bias");
     TORCH_CHECK(bias_t.dim() == 1 && bias_t.size(0) == m, "torch_sputnik.", op,
                 ": bias must have m elements (it is indexed by output row)");
     bias_ptr = bias_t.data_ptr<float>();
@@ -116,6 +284,13 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values,
   // `left_spmm` is always 3-D (src/left_replicated_spmm.cu:30).
   torch::Tensor out = (left || replicas != 1) ? torch::empty({replicas, m, n}, options)
                                               : torch::empty({m, n}, options);
+  if (auto e = get_plan(m, k, row_offsets, column_indices)) {
+    check_rc(tsp_plan_spmm_f32(e->plan, (int)n, (int)replicas, shared ? 1 : 0, row_indices.data_ptr<int>(),
+                               values.data_ptr<float>(), perm_ptr, dense.data_ptr<float>(), bias_ptr,
+                               relu ? 1 : 0, out.data_ptr<float>(), current_stream()),
+             op);
+    return out;
+  }
   check_rc(tsp_spmm_perm_f32((int)m, (int)k, (int)n, (int)nnz, (int)replicas, shared ? 1 : 0,
                              row_indices.data_ptr<int>(), values.data_ptr<float>(), perm_ptr,
                              row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
@@ -153,11 +328,11 @@ torch::Tensor spmm_bias_relu(int m, int k, torch::Tensor values, torch::Tensor r
 
 static torch::Tensor sddmm_impl(int m, int n, const torch::Tensor& row_indices_in,
                                 const torch::Tensor& row_offsets, const torch::Tensor& column_indices,
-                                const torch::Tensor& lhs, const torch::Tensor& rhs, bool reduce) {
-  TORCH_CHECK(lhs.dim() == 2 || lhs.dim() == 3, "torch_sputnik.sddmm: lhs must be 2-D or 3-D");
-  TORCH_CHECK(lhs.dim() == rhs.dim(), "torch_sputnik.sddmm: lhs and rhs must have the same rank");
-  TSP_CHECK_CUDA_F32(lhs, "lhs_matrix");
-  TSP_CHECK_CUDA_F32(rhs, "rhs_matrix");
+                                const torch::Tensor& lhs_in, const torch::Tensor& rhs_in, bool reduce) {
+  TORCH_CHECK(lhs_in.dim() == 2 || lhs_in.dim() == 3, "torch_sputnik.sddmm: lhs must be 2-D or 3-D");
+  TORCH_CHECK(lhs_in.dim() == rhs_in.dim(), "torch_sputnik.sddmm: lhs and rhs must have the same rank");
+  torch::Tensor lhs = f32_operand(lhs_in, "lhs_matrix");
+  torch::Tensor rhs = f32_operand(rhs_in, "rhs_matrix");
   c10::cuda::CUDAGuard guard(lhs.device());
   torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
   check_topology(m, row_indices, row_offsets, column_indices);
@@ -175,11 +350,19 @@ static torch::Tensor sddmm_impl(int m, int n, const torch::Tensor& row_indices_i
   auto options = torch::TensorOptions().dtype(torch::kFloat32).device(lhs.device());
   torch::Tensor out = (replicas == 1 || reduce) ? torch::empty({nnz}, options)
                                                 : torch::empty({replicas, nnz}, options);
+  const char* op = reduce ? "sddmm_reduce" : "sddmm";
+  if (auto e = get_plan(m, n, row_offsets, column_indices)) {
+    check_rc(tsp_plan_sddmm_f32(e->plan, (int)k, (int)replicas, reduce ? 1 : 0, row_indices.data_ptr<int>(),
+                                lhs.data_ptr<float>(), rhs.data_ptr<float>(), out.data_ptr<float>(),
+                                current_stream()),
+             op);
+    return out;
+  }
   auto fn = (reduce && replicas > 1) ? tsp_sddmm_reduce_f32 : tsp_sddmm_f32;
   check_rc(fn(m, (int)k, n, (int)nnz, (int)replicas, row_indices.data_ptr<int>(),
               row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(), lhs.data_ptr<float>(),
               rhs.data_ptr<float>(), out.data_ptr<float>(), current_stream()),
-           reduce ? "sddmm_reduce" : "sddmm");
+           op);
   return out;
 }
 
@@ -254,16 +437,25 @@ torch::Tensor sparse_softmax_backward(torch::Tensor y, torch::Tensor dy, torch::
   return dx;
 }
 
-static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tensor& values,
+static torch::Tensor permute_values_impl(const torch::Tensor& values, const torch::Tensor& perm) {
+  torch::Tensor out = torch::empty_like(values);
+  check_rc(tsp_permute_values_f32((int)perm.size(0), values.dim() == 2 ? (int)values.size(0) : 1,
+                                  values.data_ptr<float>(), perm.data_ptr<int>(),
+                                  out.data_ptr<float>(), current_stream()),
+           "permute_values");
+  return out;
+}
+
+static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tensor& values_in,
                                                  const torch::Tensor& row_offsets,
                                                  const torch::Tensor& column_indices,
                                                  bool want_perm) {
   // The reference handles 1-D values only (src/transpose_cuda.cu:58); its own 3-D backward
   // passes hand it [R, nnz] (modules/spmm.py:59) and get garbage.  Here [R, nnz] is permuted
   // replica by replica with the shared topology.
-  TORCH_CHECK(values.dim() == 1 || values.dim() == 2,
+  TORCH_CHECK(values_in.dim() == 1 || values_in.dim() == 2,
               "torch_sputnik.csr_transpose: values must have 1 or 2 dimensions");
-  TSP_CHECK_CUDA_F32(values, "values");
+  torch::Tensor values = f32_operand(values_in, "values");
   TSP_CHECK_CUDA_I32(row_offsets, "row_offsets");
   TSP_CHECK_CUDA_I32(column_indices, "column_indices");
   TORCH_CHECK(row_offsets.dim() == 1 && row_offsets.size(0) == m + 1,
@@ -275,7 +467,18 @@ static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tens
   c10::cuda::CUDAGuard guard(values.device());
   const int64_t replicas = values.dim() == 2 ? values.size(0) : 1;
 
-  auto fopt = torch::TensorOptions().dtype(torch::kFloat32).device(values.device());
+  // Planned topology: the sort ran once; every later call (one per backward pass in
+  // modules/spmm.py:59, sddmm.py:60, sparse_linear.py:52) is a gather through the cached
+  // permutation, and returns the plan's own index arrays -- shared between calls, do not edit.
+  if (nnz > 0) {
+    if (auto e = get_plan(m, n, row_offsets, column_indices)) {
+      ensure_transposed(e, m, n, values.device());
+      std::vector<torch::Tensor> out{permute_values_impl(values, e->perm), e->ro_t, e->ci_t};
+      if (want_perm) out.push_back(e->perm);
+      return out;
+    }
+  }
+
   auto iopt = torch::TensorOptions().dtype(torch::kInt32).device(values.device());
   torch::Tensor values_t = torch::empty_like(values);
   torch::Tensor row_offsets_t = torch::empty({n + 1}, iopt);
@@ -294,8 +497,27 @@ static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tens
            "csr_transpose");
   std::vector<torch::Tensor> out{values_t, row_offsets_t, column_indices_t};
   if (want_perm) out.push_back(perm);
-  (void)fopt;
   return out;
+}
+
+// Extension: [row_offsets_t, column_indices_t, perm, row_indices_t] of a topology from its plan
+// (row_indices_t = heaviest-first swizzle of the transpose); what a backward pass needs to multiply
+// by A^T with spmm_perm, without touching any values.
+std::vector<torch::Tensor> transposed_topology(int m, int n, torch::Tensor row_offsets, torch::Tensor column_indices) {
+  TSP_CHECK_CUDA_I32(row_offsets, "row_offsets");
+  TSP_CHECK_CUDA_I32(column_indices, "column_indices");
+  TORCH_CHECK(row_offsets.dim() == 1 && row_offsets.size(0) == m + 1,
+              "torch_sputnik.transposed_topology: expected m+1 row offsets");
+  c10::cuda::CUDAGuard guard(row_offsets.device());
+  std::shared_ptr<PlanEntry> e;
+  if (column_indices.size(0) > 0) e = get_plan(m, n, row_offsets, column_indices);
+  if (e) {
+    ensure_transposed(e, m, n, row_offsets.device());
+    return {e->ro_t, e->ci_t, e->perm, e->ri_t};
+  }
+  torch::Tensor probe = torch::empty({column_indices.size(0)}, torch::TensorOptions().dtype(torch::kFloat32).device(row_offsets.device()));
+  std::vector<torch::Tensor> t = transpose_impl(m, n, probe, row_offsets, column_indices, true);
+  return {t[1], t[2], t[3], heaviest_first(t[1])};
 }
 
 // src/sputnik.cpp:30-34 -> src/transpose_cuda.cu:45-102
@@ -318,12 +540,7 @@ torch::Tensor permute_values(torch::Tensor values, torch::Tensor perm) {
   TORCH_CHECK(perm.dim() == 1 && perm.size(0) == values.size(-1),
               "torch_sputnik.permute_values: perm must have nnz elements");
   c10::cuda::CUDAGuard guard(values.device());
-  torch::Tensor out = torch::empty_like(values);
-  check_rc(tsp_permute_values_f32((int)perm.size(0), values.dim() == 2 ? (int)values.size(0) : 1,
-                                  values.data_ptr<float>(), perm.data_ptr<int>(),
-                                  out.data_ptr<float>(), current_stream()),
-           "permute_values");
-  return out;
+  return permute_values_impl(values, perm);
 }
 
 // Extension: spmm with the transposed topology of a cached csr_transpose and the ORIGINAL values
@@ -395,9 +612,35 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("spmm_many_mask", &spmm_many_mask, "spmm with one CSR mask per batch element");
   m.def("sddmm_many_mask", &sddmm_many_mask, "sddmm with one CSR mask per batch element");
   m.def("sparse_softmax_many_mask", &sparse_softmax_many_mask, "sparse_softmax with one CSR mask per batch element");
+  m.def("sparse_softmax_many_mask_scaled", &sparse_softmax_many_mask_scaled,
+        "sparse_softmax_many_mask of scale * values");
   m.def("csr_transpose_many_mask", &csr_transpose_many_mask, "csr_transpose with one CSR mask per batch element");
   m.def("set_variant", [](const std::string& op, int v) { return tsp_set_variant(op.c_str(), v); },
         "force a kernel variant (benchmarking only)");
   m.def("launch_count", []() { return tsp_launch_count(); }, "kernels launched so far");
   m.def("abi_version", []() { return tsp_version(); });
+  m.def("transposed_topology", &transposed_topology,
+        "[row_offsets_t, column_indices_t, perm, row_indices_t] of a topology, from its cached plan");
+  m.def("plan_policy", [](int policy) {
+          PlanCache& c = plan_cache();
+          std::lock_guard<std::mutex> lock(c.mu);
+          const int old = c.policy;
+          if (policy >= 0) c.policy = policy;
+          return old;
+        },
+        "0: never plan (every call takes the unplanned C-ABI entry), 1: plan every topology on first sight "
+        "(default); negative: query.  Returns the previous policy");
+  m.def("plan_cache_clear", []() {
+          PlanCache& c = plan_cache();
+          std::lock_guard<std::mutex> lock(c.mu);
+          c.entries.clear();
+        },
+        "drop every cached plan");
+  m.def("plan_cache_stats", []() {
+          PlanCache& c = plan_cache();
+          std::lock_guard<std::mutex> lock(c.mu);
+          return std::vector<int64_t>{(int64_t)c.entries.size(), (int64_t)c.hits, (int64_t)c.misses,
+                                      (int64_t)c.evictions};
+        },
+        "[entries, hits, misses, evictions]");
 }

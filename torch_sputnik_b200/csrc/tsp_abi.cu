@@ -13,10 +13,10 @@
 #include "kernels/sddmm_gather.cuh"
 #include "kernels/spmm_gather.cuh"
 #include "kernels/spmm_staged.cuh"
-#include "kernels/sddmm_staged.cuh"
 #include "kernels/sddmm_sampled.cuh"
 #include "kernels/sddmm_rows.cuh"
 #include "kernels/attention_rows.cuh"
+#include "kernels/plan.cuh"
 
 namespace tsp {
 
@@ -81,26 +81,101 @@ int tsp_set_variant(const char* op, int variant) {
   return -1;
 }
 
-// ------------------------------------------------------------------------------------ SpMM
-int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
-                 const int* row_indices, const float* values, const int* row_offsets,
-                 const int* column_indices, const float* dense, const float* bias_or_null,
-                 int relu, float* out, void* stream_) {
-  return tsp_spmm_perm_f32(m, k, n, nnz, replicas, values_shared, row_indices, values, nullptr, row_offsets,
-                           column_indices, dense, bias_or_null, relu, out, stream_);
+// ------------------------------------------------------------------------------------ plans
+static void ephemeral_plan(tsp_plan* p, int m, int n, int nnz, const int* row_offsets, const int* column_indices) {
+  p->m = m; p->n = n; p->nnz = nnz;
+  p->row_offsets = row_offsets;
+  p->column_indices = column_indices;
+  p->ephemeral = true;
 }
 
-int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
-                      const int* row_indices, const float* values, const int* value_perm_or_null,
-                      const int* row_offsets, const int* column_indices, const float* dense,
-                      const float* bias_or_null, int relu, float* out, void* stream_) {
+int tsp_plan_create(int m, int n, int nnz, const int* row_offsets, const int* column_indices, void* stream_,
+                    tsp_plan** plan_out) {
+  if (!plan_out) return invalid("tsp_plan_create: null plan_out");
+  *plan_out = nullptr;
+  if (m < 0 || n < 0 || nnz < 0) return invalid("tsp_plan_create: negative dimension (m=%d n=%d nnz=%d)", m, n, nnz);
+  if (!row_offsets || (nnz > 0 && !column_indices)) return invalid("tsp_plan_create: null pointer argument");
+  tsp_plan* p = new tsp_plan();
+  p->m = m; p->n = n; p->nnz = nnz;
+  p->row_offsets = row_offsets;
+  p->column_indices = column_indices;
+  const int rc = plan_init_persistent(p, static_cast<cudaStream_t>(stream_));
+  if (rc != 0) {
+    plan_destroy(p);
+    return rc;
+  }
+  *plan_out = p;
+  return TSP_OK;
+}
+
+void tsp_plan_destroy(tsp_plan* plan) { plan_destroy(plan); }
+
+int tsp_plan_sorted(tsp_plan* plan) { return plan ? plan_sorted_state(plan) : -1; }
+
+int tsp_plan_transpose(tsp_plan* plan, void* stream_, tsp_plan** transposed_out, const int** row_offsets_t,
+                       const int** column_indices_t, const int** perm) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
-    return invalid("tsp_spmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k, n,
-                   nnz, replicas);
+  if (!plan || plan->ephemeral) return invalid("tsp_plan_transpose: needs a plan from tsp_plan_create");
+  std::lock_guard<std::mutex> lock(plan->mu);
+  if (!plan->transposed) {
+    if (stream_is_capturing(stream))
+      return invalid("tsp_plan_transpose: the first transpose of a topology allocates; run it once before graph capture");
+    const int m = plan->m, n = plan->n, nnz = plan->nnz;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&plan->ro_t), sizeof(int) * ((size_t)n + 1));
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&plan->ci_t), sizeof(int) * (size_t)(nnz > 0 ? nnz : 1));
+    if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&plan->perm), sizeof(int) * (size_t)(nnz > 0 ? nnz : 1));
+    void* ws = nullptr;
+    const size_t ws_bytes = tsp_csr_transpose_workspace(m, n, nnz);
+    if (e == cudaSuccess) e = cudaMalloc(&ws, ws_bytes + 256);
+    if (e != cudaSuccess) {
+      cudaFree(plan->ro_t); cudaFree(plan->ci_t); cudaFree(plan->perm); cudaFree(ws);
+      plan->ro_t = plan->ci_t = plan->perm = nullptr;
+      return cuda_fail(e, "tsp_plan_transpose (buffers)");
+    }
+    int rc = tsp_csr_transpose_f32(m, n, nnz, 0, nullptr, plan->row_offsets, plan->column_indices, nullptr,
+                                   plan->ro_t, plan->ci_t, plan->perm, ws, ws_bytes + 256, stream_);
+    if (rc == TSP_OK) {
+      tsp_plan* t = nullptr;
+      rc = tsp_plan_create(n, m, nnz, plan->ro_t, plan->ci_t, stream_, &t);
+      plan->transposed = t;
+    }
+    if (rc == TSP_OK) {
+      plan->t_stream = stream;
+      if (cudaEventCreateWithFlags(&plan->ev_t, cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventRecord(plan->ev_t, stream) != cudaSuccess) {
+        (void)cudaGetLastError();
+        cudaStreamSynchronize(stream);
+        plan->t_settled = true;
+      }
+    }
+    cudaFree(ws);   // waits for the sort kernels that use it
+    if (rc != TSP_OK) return rc;
+  }
+  if (!plan->t_settled && stream != plan->t_stream) {
+    if (cudaEventQuery(plan->ev_t) == cudaSuccess) {
+      plan->t_settled = true;
+    } else {
+      (void)cudaGetLastError();
+      cudaStreamWaitEvent(stream, plan->ev_t, 0);
+    }
+  }
+  if (transposed_out) *transposed_out = plan->transposed;
+  if (row_offsets_t) *row_offsets_t = plan->ro_t;
+  if (column_indices_t) *column_indices_t = plan->ci_t;
+  if (perm) *perm = plan->perm;
+  return TSP_OK;
+}
+
+// ------------------------------------------------------------------------------------ SpMM
+static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, const int* row_indices,
+                     const float* values, const int* value_perm_or_null, const float* dense,
+                     const float* bias_or_null, int relu, float* out, cudaStream_t stream) {
+  const int m = plan->m, k = plan->n, nnz = plan->nnz;
+  if (n < 0 || replicas < 0)
+    return invalid("tsp_spmm_f32: negative dimension (n=%d replicas=%d)", n, replicas);
   if (replicas > 65535) return invalid("tsp_spmm_f32: replicas=%d exceeds 65535", replicas);
   if (m == 0 || n == 0 || replicas == 0) return TSP_OK;
-  if (!row_offsets || !out || (nnz > 0 && (!values || !column_indices || !dense)))
+  if (!plan->row_offsets || !out || (nnz > 0 && (!values || !plan->column_indices || !dense)))
     return invalid("tsp_spmm_f32: null pointer argument");
 
   SpmmArgs a;
@@ -108,8 +183,8 @@ int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_sha
   a.values_stride = values_shared ? 0 : (long long)nnz;
   a.row_indices = row_indices;
   a.values = values;
-  a.row_offsets = row_offsets;
-  a.column_indices = column_indices;
+  a.row_offsets = plan->row_offsets;
+  a.column_indices = plan->column_indices;
   a.dense = dense;
   a.bias = bias_or_null;
   a.relu = relu;
@@ -124,13 +199,27 @@ int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_sha
   // variant: 0 = heuristic, 1 = gather, 2 = staged (rows per group from density), 3 = staged with
   // 4-row groups, 4 = staged with 8-row groups.
   const double density = (double)nnz / ((double)m * (double)k);
+  // Below ~22 % density (measured crossover on B200, profiles/) rows of a group share almost no columns, merging cannot raise the FMA
+  // per shared-memory wavefront ratio, and the L1/L2 gather kernel has less fixed cost per slab.
   const bool staged_ok = variant != 1 && spmm_staged_applicable(a, replicas) &&
                          (variant != 0 || density >= 0.22);
   if (staged_ok) {
-    // Below ~22 % density (measured crossover on B200, profiles/) rows of a group share almost no columns, merging cannot raise the FMA
-    // per shared-memory wavefront ratio, and the L1/L2 gather kernel has less fixed cost per slab.
-    const int rc = launch_spmm_staged(a, replicas, stream, variant == 3 ? 4 : (variant == 4 ? 8 : 0));
-    if (rc >= 0) return rc;  // < 0: staged path declined, use the gather kernel
+    StagedGuard guard;
+    int rc = 0;
+    const int gs = plan_guard(plan, stream, &guard, &rc);
+    if (rc != 0) return rc;
+    if (gs != kGuardUnsorted) {
+      if ((rc = plan_flush_check(plan, stream)) != 0) return rc;
+      rc = launch_spmm_staged(a, replicas, stream, guard, variant == 3 ? 4 : (variant == 4 ? 8 : 0));
+      if (rc != 0) return rc;
+      if (gs == kGuardSorted) return TSP_OK;
+      // Verdict not on the host yet: the same arguments go through the gather kernel, which exits
+      // at once unless the check raised the plan's flag.
+      a.guard_flag = guard.flag;
+      launch_spmm_gather<4, 2>(a, replicas, stream);
+      TSP_CHECK_LAUNCH("tsp_spmm_f32 (gather fallback)");
+      return TSP_OK;
+    }
   }
   if (vec4_ok && n > 128) {
     launch_spmm_gather<4, 2>(a, replicas, stream);
@@ -149,6 +238,38 @@ int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_sha
   return TSP_OK;
 }
 
+int tsp_plan_spmm_f32(tsp_plan* plan, int n, int replicas, int values_shared, const int* row_indices,
+                      const float* values, const int* value_perm_or_null, const float* dense,
+                      const float* bias_or_null, int relu, float* out, void* stream) {
+  if (!plan) return invalid("tsp_plan_spmm_f32: null plan");
+  return spmm_core(plan, n, replicas, values_shared, row_indices, values, value_perm_or_null, dense,
+                   bias_or_null, relu, out, static_cast<cudaStream_t>(stream));
+}
+
+int tsp_spmm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
+                 const int* row_indices, const float* values, const int* row_offsets,
+                 const int* column_indices, const float* dense, const float* bias_or_null,
+                 int relu, float* out, void* stream_) {
+  return tsp_spmm_perm_f32(m, k, n, nnz, replicas, values_shared, row_indices, values, nullptr, row_offsets,
+                           column_indices, dense, bias_or_null, relu, out, stream_);
+}
+
+int tsp_spmm_perm_f32(int m, int k, int n, int nnz, int replicas, int values_shared,
+                      const int* row_indices, const float* values, const int* value_perm_or_null,
+                      const int* row_offsets, const int* column_indices, const float* dense,
+                      const float* bias_or_null, int relu, float* out, void* stream_) {
+  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_spmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k, n,
+                   nnz, replicas);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  tsp_plan eph;
+  ephemeral_plan(&eph, m, k, nnz, row_offsets, column_indices);
+  const int rc = spmm_core(&eph, n, replicas, values_shared, row_indices, values, value_perm_or_null, dense,
+                           bias_or_null, relu, out, stream);
+  plan_release_ephemeral(&eph, stream);
+  return rc;
+}
+
 // ----------------------------------------------------------------------------------- SDDMM
 static void launch_sddmm_gather_any(const SddmmArgs& a, int replicas, cudaStream_t stream) {
   const int k = a.k;
@@ -164,47 +285,65 @@ static void launch_sddmm_gather_any(const SddmmArgs& a, int replicas, cudaStream
   }
 }
 
-static int sddmm_impl(int m, int k, int n, int nnz, int replicas, const int* row_indices,
-                      const int* row_offsets, const int* column_indices, const float* lhs,
-                      const float* rhs, float* out, void* stream_, bool reduce) {
+// The staged SDDMM kernels (tiled: dense register tiles; sampled: TMA-staged operands, only the
+// sampled products).  Returns  0: a staged kernel wrote out[] for certain (columns known sorted);
+// 1: a staged kernel was launched under the plan's device guard -- the caller queues the guarded
+// gather launch behind it (a.guard_flag is set);  -1: no staged kernel launched;  > 1: error code + 1.
+static int sddmm_staged(tsp_plan* plan, SddmmArgs& a, int replicas, cudaStream_t stream, bool want_tiled,
+                        bool tiled_v1, bool want_sampled) {
+  const bool tiled = want_tiled && sddmm_tiled_applicable(a, replicas);
+  const bool sampled = !tiled && want_sampled && sddmm_sampled_applicable(a, replicas);
+  if (!tiled && !sampled) return -1;
+  StagedGuard guard;
+  int rc = 0;
+  const int gs = plan_guard(plan, stream, &guard, &rc);
+  if (rc != 0) return rc + 1;
+  if (gs == kGuardUnsorted) return -1;
+  const int bn = sampled ? sddmm_sampled_pick_bn(a, replicas, g_sddmm_bn.load(), g_sddmm_p.load()) : 0;
+  const void* view = plan_view(plan, tiled ? kBitmapKey : bn, stream, &rc);
+  if (rc != 0) return rc + 1;
+  if (!view) return -1;
+  if ((rc = plan_flush_check(plan, stream)) != 0) return rc + 1;
+  rc = tiled ? launch_sddmm_tiled(a, replicas, stream, guard, view, tiled_v1)
+             : launch_sddmm_sampled(a, replicas, stream, guard, bn, static_cast<const int*>(view), g_sddmm_p.load());
+  if (rc != 0) return rc + 1;
+  if (gs == kGuardSorted) return 0;
+  a.guard_flag = guard.flag;
+  return 1;
+}
+
+static int sddmm_core(tsp_plan* plan, int k, int replicas, const int* row_indices, const float* lhs,
+                      const float* rhs, float* out, cudaStream_t stream, bool reduce) {
   (void)row_indices;  // the flat-nonzero decomposition is balanced without a row swizzle
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
-    return invalid("tsp_sddmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k,
-                   n, nnz, replicas);
+  const int m = plan->m, n = plan->n, nnz = plan->nnz;
+  if (k < 0 || replicas < 0) return invalid("tsp_sddmm_f32: negative dimension (k=%d replicas=%d)", k, replicas);
   if (replicas > 65535) return invalid("tsp_sddmm_f32: replicas=%d exceeds 65535", replicas);
   if (nnz == 0 || replicas == 0) return TSP_OK;
-  if (!row_offsets || !column_indices || !out || (k > 0 && (!lhs || !rhs)))
+  if (!plan->row_offsets || !plan->column_indices || !out || (k > 0 && (!lhs || !rhs)))
     return invalid("tsp_sddmm_f32: null pointer argument");
 
   SddmmArgs a;
   a.m = m; a.k = k; a.n = n; a.nnz = nnz;
-  a.row_offsets = row_offsets;
-  a.column_indices = column_indices;
+  a.row_offsets = plan->row_offsets;
+  a.column_indices = plan->column_indices;
   a.lhs = lhs;
   a.rhs = rhs;
   a.out = out;
+  const double density = (double)nnz / ((double)m * (double)n);
+  const int variant = g_sddmm_variant.load();
   if (reduce) {
     // out[j] = sum over replicas: only the staged kernels fold the replica loop into their k loop;
     // anything else computes [replicas, nnz] into stream-ordered scratch and sums it.
-    const double dens = (double)nnz / ((double)m * (double)n);
     a.reduce_reps = replicas;
-    StagedGuard guard;
-    int rc = -1;
-    const int forced = g_sddmm_variant.load();   // 1: no staged kernel (benchmark knob)
-    if (forced == 1) rc = -1;
-    else if (dens >= 0.22 && sddmm_tiled_applicable(a, replicas)) rc = launch_sddmm_tiled(a, replicas, stream, &guard, false);
-    else if (dens >= 0.015 && sddmm_sampled_applicable(a, replicas))
-      rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load(), g_sddmm_p.load());
-    if (rc > 0) return rc;
-    if (rc == 0) {
-      // The staged kernel wrote out[] unless the columns turned out unsorted; in that case the
-      // guarded gather kernel below (which exits at once otherwise) redoes the work, with the
-      // replica loop inside it.
-      SddmmArgs f = a;
-      f.guard_slot = guard.slot;
-      f.guard_id = guard.call_id;
-      launch_sddmm_gather_any(f, replicas, stream);
+    // variant 1: no staged kernel (benchmark knob)
+    const int st = variant == 1 ? -1 : sddmm_staged(plan, a, replicas, stream, density >= 0.22, false, density >= 0.015);
+    if (st > 1) return st - 1;
+    if (st == 0) return TSP_OK;
+    if (st == 1) {
+      // The staged kernel wrote out[] unless the columns turn out unsorted; in that case the
+      // guarded gather kernel (which exits at once otherwise) redoes the work, with the replica
+      // loop inside it.
+      launch_sddmm_gather_any(a, replicas, stream);
       TSP_CHECK_LAUNCH("tsp_sddmm_reduce_f32 (gather fallback)");
       return TSP_OK;
     }
@@ -212,10 +351,9 @@ static int sddmm_impl(int m, int k, int n, int nnz, int replicas, const int* row
     float* scratch = nullptr;
     cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&scratch), sizeof(float) * (size_t)replicas * nnz, stream);
     if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_reduce_f32 (scratch)");
-    int rc2 = sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, scratch,
-                         stream_, false);
+    int rc2 = sddmm_core(plan, k, replicas, row_indices, lhs, rhs, scratch, stream, false);
     if (rc2 == TSP_OK) {
-      reduce_replicas_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(scratch, nnz, replicas, out, 0, 0u);
+      reduce_replicas_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(scratch, nnz, replicas, out);
       g_launches.fetch_add(1, std::memory_order_relaxed);
       if (cudaGetLastError() != cudaSuccess) rc2 = TSP_ERR_CUDA;
     }
@@ -226,8 +364,6 @@ static int sddmm_impl(int m, int k, int n, int nnz, int replicas, const int* row
   // variant: 0 = heuristic, 1 = gather, 2 = tiled (dense register tiles, sampled), 3 = sampled
   // (TMA-staged operands, only the sampled products), 4 = tiled v1,
   // 5 = rows (k <= 128).
-  const int variant = g_sddmm_variant.load();
-  const double density = (double)nnz / ((double)m * (double)n);
   const bool want_tiled = variant == 2 || variant == 4 || (variant == 0 && density >= 0.22);   // 4 = tiled v1
   const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.22);
   // 5 = rows (short inner dimension, k <= 128): no sortedness requirement, no fallback needed.
@@ -236,35 +372,45 @@ static int sddmm_impl(int m, int k, int n, int nnz, int replicas, const int* row
     TSP_CHECK_LAUNCH("tsp_sddmm_f32 (rows)");
     return TSP_OK;
   }
-  if (want_tiled && sddmm_tiled_applicable(a, replicas)) {
-    StagedGuard guard;
-    const int rc = launch_sddmm_tiled(a, replicas, stream, &guard, variant == 4);
-    if (rc != 0) return rc;
-    a.guard_slot = guard.slot;   // the gather launch below becomes the unsorted-columns fallback
-    a.guard_id = guard.call_id;
-  } else if (want_sampled && sddmm_sampled_applicable(a, replicas)) {
-    StagedGuard guard;
-    const int rc = launch_sddmm_sampled(a, replicas, stream, &guard, g_sddmm_bn.load(), g_sddmm_p.load());
-    if (rc != 0) return rc;
-    a.guard_slot = guard.slot;
-    a.guard_id = guard.call_id;
-  }
-
-  launch_sddmm_gather_any(a, replicas, stream);
+  const int st = sddmm_staged(plan, a, replicas, stream, want_tiled, variant == 4, want_sampled);
+  if (st > 1) return st - 1;
+  if (st == 0) return TSP_OK;
+  launch_sddmm_gather_any(a, replicas, stream);   // st == 1: guarded fallback; st == -1: the kernel
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (gather)");
   return TSP_OK;
+}
+
+int tsp_plan_sddmm_f32(tsp_plan* plan, int k, int replicas, int reduce, const int* row_indices,
+                       const float* lhs, const float* rhs, float* out, void* stream) {
+  if (!plan) return invalid("tsp_plan_sddmm_f32: null plan");
+  return sddmm_core(plan, k, replicas, row_indices, lhs, rhs, out, static_cast<cudaStream_t>(stream),
+                    reduce != 0 && replicas > 1);
+}
+
+static int sddmm_unplanned(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                           const int* row_offsets, const int* column_indices, const float* lhs,
+                           const float* rhs, float* out, void* stream_, bool reduce) {
+  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_sddmm_f32: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k,
+                   n, nnz, replicas);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  tsp_plan eph;
+  ephemeral_plan(&eph, m, n, nnz, row_offsets, column_indices);
+  const int rc = sddmm_core(&eph, k, replicas, row_indices, lhs, rhs, out, stream, reduce);
+  plan_release_ephemeral(&eph, stream);
+  return rc;
 }
 
 int tsp_sddmm_f32(int m, int k, int n, int nnz, int replicas, const int* row_indices,
                   const int* row_offsets, const int* column_indices, const float* lhs,
                   const float* rhs, float* out, void* stream) {
-  return sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, out, stream, false);
+  return sddmm_unplanned(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, out, stream, false);
 }
 
 int tsp_sddmm_reduce_f32(int m, int k, int n, int nnz, int replicas, const int* row_indices,
                          const int* row_offsets, const int* column_indices, const float* lhs,
                          const float* rhs, float* out, void* stream) {
-  return sddmm_impl(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, out, stream, true);
+  return sddmm_unplanned(m, k, n, nnz, replicas, row_indices, row_offsets, column_indices, lhs, rhs, out, stream, true);
 }
 
 // --------------------------------------------------------------------------------- softmax
@@ -381,7 +527,7 @@ int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* valu
   if (m < 0 || n < 0 || nnz < 0 || replicas < 0)
     return invalid("tsp_csr_transpose_f32: negative dimension");
   if (!row_offsets_t) return invalid("tsp_csr_transpose_f32: null row_offsets_t");
-  if (nnz > 0 && (!values || !row_offsets || !column_indices || !values_t || !column_indices_t))
+  if (nnz > 0 && (!row_offsets || !column_indices || !column_indices_t || (replicas > 0 && (!values || !values_t))))
     return invalid("tsp_csr_transpose_f32: null pointer argument");
   if (nnz == 0) {
     fill_int_kernel<<<ceil_div(n + 1, 256), 256, 0, stream>>>(row_offsets_t, n + 1, 0);

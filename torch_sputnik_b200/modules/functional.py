@@ -38,26 +38,22 @@ def dense_to_sparse(matrix: torch.Tensor):
 
 
 class TransposedTopology:
-    """CSC view of a static CSR topology: (row_offsets_t, column_indices_t, row_indices_t, perm)."""
+    """CSC view of a static CSR topology: (row_offsets_t, column_indices_t, row_indices_t, perm).
+
+    Comes from the topology's plan inside the extension (``ops.transposed_topology``): the stable
+    sort runs once per topology, the plan cache holds the index tensors it is keyed on (so a freed
+    address cannot be mistaken for a live topology) and compares their version counters on every
+    lookup (so an in-place edit plans again)."""
+
+    __slots__ = ("row_offsets", "column_indices", "perm", "row_indices")
 
     def __init__(self, m, n, row_offsets, column_indices):
-        probe = torch.empty(column_indices.shape[0], dtype=torch.float32, device=column_indices.device)
-        _, self.row_offsets, self.column_indices, self.perm = ops.csr_transpose_with_perm(
-            m, n, probe, row_offsets, column_indices)
-        self.row_indices = diffsort(self.row_offsets)
+        self.row_offsets, self.column_indices, self.perm, self.row_indices = ops.transposed_topology(
+            m, n, row_offsets, column_indices)
 
     @classmethod
     def get(cls, m, n, row_offsets, column_indices) -> "TransposedTopology":
-        """Cached on the row_offsets tensor itself, so it lives exactly as long as the topology;
-        keyed on the partner tensor and both version counters (in-place edits invalidate)."""
-        store = row_offsets.__dict__.setdefault("_tsp_transposed", {})
-        key = (m, n, column_indices.data_ptr(), column_indices.shape[0], row_offsets._version,
-               column_indices._version)
-        hit = store.get(key)
-        if hit is None:
-            store.clear()
-            hit = store[key] = cls(m, n, row_offsets, column_indices)
-        return hit
+        return cls(m, n, row_offsets, column_indices)
 
 
 class Spmm(torch.autograd.Function):
@@ -94,6 +90,9 @@ class Spmm(torch.autograd.Function):
             grad_dense = ops.spmm_perm(k, m, values.contiguous(), t.perm, t.row_indices, t.row_offsets,
                                        t.column_indices, grad_output)
             grad_dense = grad_dense.reshape(dense.shape)
+        if grad_values is not None:
+            # one replica: sddmm follows the reference and returns [nnz] for a [1, nnz] input (src/sddmm_cuda.cu:43)
+            grad_values = grad_values.reshape(values.shape)
         return None, None, grad_values, None, None, None, grad_dense
 
 
@@ -210,11 +209,8 @@ def many_mask_attention(query, key, value, topo: ManyMaskTopology, scale: float)
     if not (torch.is_grad_enabled() and (q3.requires_grad or k3.requires_grad or v3.requires_grad)):
         scores = ops.sddmm_many_mask(b, topo.m, topo.n, topo.nonzeros, topo.row_indices, topo.row_offsets,
                                      topo.column_indices, q3, k3)
-        # the scale is folded into the scores' left operand: softmax(scale * x) has no many-mask entry
-        if scale != 1.0:
-            scores = scores * scale
-        probs = ops.sparse_softmax_many_mask(b, topo.m, topo.nonzeros, scores, topo.row_indices,
-                                             topo.row_offsets, topo.column_indices)
+        probs = ops.sparse_softmax_many_mask_scaled(b, topo.m, topo.nonzeros, scores, topo.row_indices,
+                                                    topo.row_offsets, topo.column_indices, float(scale))
         return ops.spmm_many_mask(b, topo.m, topo.n, topo.nonzeros, probs, topo.row_indices, topo.row_offsets,
                                   topo.column_indices, v3)
     outs = []
