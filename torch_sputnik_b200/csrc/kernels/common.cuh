@@ -1,6 +1,8 @@
 // common.cuh -- shared device/host helpers for the tsp kernels (sm_100a only).
 #pragma once
 
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -182,6 +184,107 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const void* tmap, in
       "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(smem_dst)),
       "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
       : "memory");
+}
+
+// ---- storage types: fp32, or fp16 / bf16 storage with fp32 arithmetic (the
+// reference's half SpMM, cuda_spmm.cu.cc:511-570, keeps fp32 accumulators the same way) -------------
+template <typename T>
+struct Elem;
+template <>
+struct Elem<float> {
+  static constexpr int kPer16 = 4;   // elements per 16-byte vector
+  __device__ __forceinline__ static float to_f(float x) { return x; }
+  __device__ __forceinline__ static float from_f(float x) { return x; }
+};
+template <>
+struct Elem<__half> {
+  static constexpr int kPer16 = 8;
+  __device__ __forceinline__ static float to_f(__half x) { return __half2float(x); }
+  __device__ __forceinline__ static __half from_f(float x) { return __float2half_rn(x); }
+};
+template <>
+struct Elem<__nv_bfloat16> {
+  static constexpr int kPer16 = 8;
+  __device__ __forceinline__ static float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
+  __device__ __forceinline__ static __nv_bfloat16 from_f(float x) { return __float2bfloat16_rn(x); }
+};
+
+// two packed 16-bit elements -> two floats
+template <typename T>
+__device__ __forceinline__ float2 unpack_pair(unsigned w);
+template <>
+__device__ __forceinline__ float2 unpack_pair<__half>(unsigned w) {
+  return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
+template <>
+__device__ __forceinline__ float2 unpack_pair<__nv_bfloat16>(unsigned w) {
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));   // bf16 = top half of fp32
+}
+template <typename T>
+__device__ __forceinline__ unsigned pack_pair(float lo, float hi);
+template <>
+__device__ __forceinline__ unsigned pack_pair<__half>(float lo, float hi) {
+  const __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const unsigned*>(&h);
+}
+template <>
+__device__ __forceinline__ unsigned pack_pair<__nv_bfloat16>(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const unsigned*>(&h);
+}
+
+// E consecutive elements of T at p (aligned to E * sizeof(T)) -> fp32, one read-only vector load.
+template <typename T, int E>
+__device__ __forceinline__ void load_elems(float (&dst)[E], const T* p) {
+  if constexpr (sizeof(T) == 4) {
+    static_assert(E == 1 || E == 2 || E == 4, "fp32: 1, 2 or 4 elements per load");
+    if constexpr (E == 4) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+      dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+    } else if constexpr (E == 2) {
+      const float2 v = __ldg(reinterpret_cast<const float2*>(p));
+      dst[0] = v.x; dst[1] = v.y;
+    } else {
+      dst[0] = __ldg(reinterpret_cast<const float*>(p));
+    }
+  } else {
+    static_assert(E == 1 || E == 2 || E == 4 || E == 8, "16-bit: 1, 2, 4 or 8 elements per load");
+    if constexpr (E == 8) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+      const float2 a = unpack_pair<T>(v.x), b = unpack_pair<T>(v.y), c = unpack_pair<T>(v.z), d = unpack_pair<T>(v.w);
+      dst[0] = a.x; dst[1] = a.y; dst[2] = b.x; dst[3] = b.y; dst[4] = c.x; dst[5] = c.y; dst[6] = d.x; dst[7] = d.y;
+    } else if constexpr (E == 4) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+      const float2 a = unpack_pair<T>(v.x), b = unpack_pair<T>(v.y);
+      dst[0] = a.x; dst[1] = a.y; dst[2] = b.x; dst[3] = b.y;
+    } else if constexpr (E == 2) {
+      const float2 a = unpack_pair<T>(__ldg(reinterpret_cast<const unsigned*>(p)));
+      dst[0] = a.x; dst[1] = a.y;
+    } else {
+      const unsigned short raw = __ldg(reinterpret_cast<const unsigned short*>(p));
+      dst[0] = unpack_pair<T>((unsigned)raw).x;
+    }
+  }
+}
+
+// fp32 -> E consecutive elements of T at p (round to nearest even), one vector store.
+template <typename T, int E>
+__device__ __forceinline__ void store_elems(T* p, const float (&src)[E]) {
+  if constexpr (sizeof(T) == 4) {
+    if constexpr (E == 4) *reinterpret_cast<float4*>(p) = make_float4(src[0], src[1], src[2], src[3]);
+    else if constexpr (E == 2) *reinterpret_cast<float2*>(p) = make_float2(src[0], src[1]);
+    else *reinterpret_cast<float*>(p) = src[0];
+  } else {
+    if constexpr (E == 8)
+      *reinterpret_cast<uint4*>(p) = make_uint4(pack_pair<T>(src[0], src[1]), pack_pair<T>(src[2], src[3]),
+                                                pack_pair<T>(src[4], src[5]), pack_pair<T>(src[6], src[7]));
+    else if constexpr (E == 4)
+      *reinterpret_cast<uint2*>(p) = make_uint2(pack_pair<T>(src[0], src[1]), pack_pair<T>(src[2], src[3]));
+    else if constexpr (E == 2)
+      *reinterpret_cast<unsigned*>(p) = pack_pair<T>(src[0], src[1]);
+    else
+      *p = Elem<T>::from_f(src[0]);
+  }
 }
 
 #endif  // __CUDACC__

@@ -17,17 +17,19 @@
 
 namespace tsp {
 
-struct SpmmArgs {
+// T: storage type of values / dense / out (float, __half, __nv_bfloat16); arithmetic is fp32.
+template <typename T>
+struct SpmmArgsT {
   int m, k, n, nnz;
   long long values_stride;  // nnz, or 0 when one values vector is shared by all replicas
   const int* row_indices;   // may be null (identity)
-  const float* values;
+  const T* values;
   const int* row_offsets;
   const int* column_indices;
-  const float* dense;
-  const float* bias;  // may be null
+  const T* dense;
+  const float* bias;  // may be null; always fp32 (as sputnik::CudaSpmmBiasRelu, cuda_spmm.h:64-72,115-127)
   int relu;
-  float* out;
+  T* out;
   // value_perm != null: nonzero p takes values[value_perm[p]] -- the CSR arrays describe the
   // TRANSPOSE of the matrix the values are stored for (perm from tsp_csr_transpose_f32), so a
   // backward pass multiplies by A^T without materialising the permuted [replicas, nnz] values.
@@ -36,6 +38,7 @@ struct SpmmArgs {
   // only if the sorted-columns check raised *guard_flag (a device word owned by the call's plan).
   const unsigned* guard_flag = nullptr;
 };
+using SpmmArgs = SpmmArgsT<float>;
 
 // "Columns are not sorted" verdict of ONE topology: a device word owned by the topology's plan
 // (plan.cuh) -- persistent for a planned topology, stream-ordered scratch for an unplanned call.
