@@ -174,6 +174,39 @@ int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int
                            float* values_t, void* stream);
 
 /*
+ * 16-bit storage, fp32 arithmetic.  Replaces
+ * sputnik::CudaSpmm / CudaSpmmBiasRelu (half2 values, short2 indices, half2 dense; float bias)
+ * third_party/sputnik/sputnik/spmm/cuda_spmm.cu.cc:511-570, contract cuda_spmm.h:75-127 -- which the
+ * reference binding never reaches (src/spmm_cuda.cu:41-55 hard-codes float) -- and extends the same
+ * storage contract to SDDMM and the CSR softmax, which Sputnik has in fp32 only.  values / dense /
+ * lhs / rhs / out point at IEEE fp16 (..._f16) or bfloat16 (..._bf16) elements; indices stay int32
+ * (no short2 packing, so k is not limited to 32767), any nnz per row, any n (16-byte-aligned rows
+ * take the 8-element vector path).  Every product and sum is fp32, each result is rounded to the
+ * storage type once.  bias stays fp32.  Argument meaning otherwise as tsp_spmm_perm_f32 /
+ * tsp_sddmm_f32 / tsp_csr_softmax_f32.  tsp_permute_values_b16 moves any 16-bit element type.
+ */
+int tsp_spmm_f16(int m, int k, int n, int nnz, int replicas, int values_shared,
+                 const int* row_indices, const void* values, const int* value_perm_or_null,
+                 const int* row_offsets, const int* column_indices, const void* dense,
+                 const float* bias_or_null, int relu, void* out, void* stream);
+int tsp_spmm_bf16(int m, int k, int n, int nnz, int replicas, int values_shared,
+                  const int* row_indices, const void* values, const int* value_perm_or_null,
+                  const int* row_offsets, const int* column_indices, const void* dense,
+                  const float* bias_or_null, int relu, void* out, void* stream);
+int tsp_sddmm_f16(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                  const int* row_offsets, const int* column_indices, const void* lhs,
+                  const void* rhs, void* out, void* stream);
+int tsp_sddmm_bf16(int m, int k, int n, int nnz, int replicas, const int* row_indices,
+                   const int* row_offsets, const int* column_indices, const void* lhs,
+                   const void* rhs, void* out, void* stream);
+int tsp_csr_softmax_f16(int m, int nnz, int replicas, float scale, const void* values,
+                        const int* row_indices, const int* row_offsets, void* out, void* stream);
+int tsp_csr_softmax_bf16(int m, int nnz, int replicas, float scale, const void* values,
+                         const int* row_indices, const int* row_offsets, void* out, void* stream);
+int tsp_permute_values_b16(int nnz, int replicas, const void* values, const int* perm,
+                           void* values_t, void* stream);
+
+/*
  * Per-topology plans ("optional transpose-plan cache"; the reference's
  * topology is fixed at module construction, modules/sparse_attention.py:49-52,
  * modules/sparse_linear.py:78-83, and its binding redoes the topology work on every call,

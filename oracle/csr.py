@@ -100,6 +100,17 @@ def random_csr(m: int, k: int, density: float | None = None, *, nnz: int | None 
     return Csr(m, k, vals, ri, row_offsets, cols)
 
 
+def even_rows(a: Csr) -> Csr:
+    """Drop the last nonzero of every odd-length row: the layout constraint of the reference's half
+    SpMM (third_party/sputnik/sputnik/spmm/cuda_spmm.h:75-113: half2 values, short2 indices)."""
+    lens = np.diff(a.row_offsets)
+    keep = np.ones(a.values.shape[0], dtype=bool)
+    odd = np.flatnonzero(lens % 2 == 1)
+    keep[a.row_offsets[odd + 1] - 1] = False
+    ro = np.concatenate([[0], np.cumsum(lens - (lens % 2))]).astype(np.int32)
+    return Csr(a.m, a.k, a.values[keep], sorted_row_swizzle(ro), ro, a.column_indices[keep])
+
+
 def dense_operand(shape, seed: int, dist: str = "u01") -> np.ndarray:
     rng = np.random.default_rng(seed)
     x = rng.random(shape, dtype=np.float32)

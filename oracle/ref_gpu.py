@@ -25,6 +25,7 @@ def _load():
         lib = ctypes.CDLL(LIB_PATH)
         i, vp, sz = ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
         lib.ref_spmm.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp]
+        lib.ref_spmm_half.argtypes = [i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.ref_sddmm.argtypes = [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
         lib.ref_sparse_softmax.argtypes = [i, i, i, vp, vp, vp, vp, vp, vp]
         lib.ref_csr_transpose.argtypes = [i, i, i, vp, vp, vp, vp, vp, vp, vp]
@@ -58,6 +59,25 @@ def spmm(m, k, values, row_indices, row_offsets, column_indices, dense, bias=Non
     if rc != 0:
         raise RuntimeError(f"ref_spmm failed: cudaError {rc}")
     return out if dense.dim() == 3 else out[0]
+
+
+def spmm_half(m, k, values, row_indices, row_offsets, column_indices, dense, bias=None):
+    """sputnik::CudaSpmm / CudaSpmmBiasRelu, half2 / short2 overloads (cuda_spmm.cu.cc:511-570).
+    values, dense: float16; column_indices: int32 (narrowed to the int16 the kernel reads).  The
+    contract of cuda_spmm.h:75-113 is asserted: even nonzero count in every row, n % 4 == 0 (half4 dense loads, cuda_spmm.cu.cc:548-553), k < 32768."""
+    import torch
+    lib = _load()
+    n = dense.shape[-1]
+    nnz = column_indices.shape[0]
+    assert values.dtype == torch.float16 and dense.dtype == torch.float16 and dense.dim() == 2
+    assert n % 4 == 0 and k < 32768 and bool((row_offsets % 2 == 0).all()), "cuda_spmm.h:75-113"
+    cols16 = column_indices.to(torch.int16).contiguous()
+    out = torch.zeros((m, n), dtype=torch.float16, device=dense.device)
+    rc = lib.ref_spmm_half(m, k, n, nnz, _p(row_indices), _p(values), _p(row_offsets), _p(cols16), _p(dense),
+                           _p(bias), _p(out), _stream())
+    if rc != 0:
+        raise RuntimeError(f"ref_spmm_half failed: cudaError {rc}")
+    return out
 
 
 def sddmm(m, n, row_indices, row_offsets, column_indices, lhs, rhs):

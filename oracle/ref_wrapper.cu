@@ -7,6 +7,7 @@
 // SparseSoftmax (the symbols src/*.cu of the reference binds) and to cuSPARSE's
 // cusparseCsr2cscEx2(ALG1) exactly as src/transpose_cuda.cu:22-31,90-99 calls it, reproducing
 // the binding's per-replica host loop (src/spmm_cuda.cu:48-57).
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <cusparse.h>
 
@@ -31,6 +32,25 @@ int ref_spmm(int m, int k, int n, int nnz, int replicas, int values_shared, cons
     if (e != cudaSuccess) return (int)e;
   }
   return 0;
+}
+
+// The reference's half-precision SpMM (cuda_spmm.cu.cc:511-570; contract cuda_spmm.h:75-127: every
+// row holds an even number of nonzeros, n is even, column indices are 16-bit).  The Torch-Sputnik
+// binding never reaches it (src/spmm_cuda.cu:41-55 hard-codes float); it pins the 16-bit entry points.
+int ref_spmm_half(int m, int k, int n, int nnz, const int* row_indices, const void* values,
+                  const int* row_offsets, const void* column_indices_i16, const void* dense,
+                  const float* bias_or_null, void* out, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e;
+  if (bias_or_null)
+    e = sputnik::CudaSpmmBiasRelu(m, k, n, nnz, row_indices, static_cast<const half2*>(values), row_offsets,
+                                  static_cast<const short2*>(column_indices_i16), static_cast<const half2*>(dense),
+                                  bias_or_null, static_cast<half2*>(out), s);
+  else
+    e = sputnik::CudaSpmm(m, k, n, nnz, row_indices, static_cast<const half2*>(values), row_offsets,
+                          static_cast<const short2*>(column_indices_i16), static_cast<const half2*>(dense),
+                          static_cast<half2*>(out), s);
+  return (int)e;
 }
 
 int ref_sddmm(int m, int k, int n, int nnz, int replicas, const int* row_indices,

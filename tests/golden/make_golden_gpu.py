@@ -13,6 +13,13 @@ its inputs (so nothing depends on RNG stability) and the reference's outputs:
   sddmm_*     sputnik::CudaSddmm                     (src/sddmm_cuda.cu:45-54)
   softmax_*   sputnik::SparseSoftmax                 (src/softmax_cuda.cu:35-43)
   transpose_* cusparseCsr2cscEx2(ALG1)               (src/transpose_cuda.cu:90-99)
+
+`python tests/golden/make_golden_gpu.py --half gpurun_out/ref_b200_f16.npz` writes the second file,
+tests/golden/ref_b200_f16.npz:
+
+  spmmh_*     sputnik::CudaSpmm / CudaSpmmBiasRelu, half2 / short2 overloads (cuda_spmm.cu.cc:511-570):
+              fp16 values and dense operand, fp32 accumulation, fp16 result; rows padded to an even
+              nonzero count as spmm_test.cu.cc:172-176 does (here: the odd entry is dropped)
 """
 import os
 import sys
@@ -48,6 +55,46 @@ SDDMM = [  # name, m, k, n, nnz/density      (sddmm_test.cu.cc:76-91)
 SOFTMAX = [("t72", 72, 72, 0.1), ("long", 16, 4096, 0.5), ("wide", 128, 4096, 0.1)]
 TRANSPOSE = [("kat4", 4, 4, 0.5), ("t72", 72, 64, 0.1), ("r300", 300, 1000, 0.02), ("tall", 1000, 37, 0.3),
              ("full", 64, 64, 1.0), ("wide", 5, 70000, 0.001), ("big", 512, 512, 0.1)]
+
+
+SPMM_HALF = [  # name, m, k, n, nnz/density, bias      (shapes: spmm_test.cu.cc:80-95; n even, k < 32768)
+    ("p0", 4, 32, 32, dict(nnz=32), False),
+    ("p1", 4, 32, 48, dict(nnz=128), False),
+    ("p2", 7, 96, 40, dict(nnz=333), False),
+    ("p3", 11, 55, 8, dict(nnz=293), False),
+    ("p4", 4, 128, 128, dict(nnz=512), False),
+    ("p5", 64, 512, 512, dict(nnz=16384), False),
+    ("b1k", 1024, 1024, 128, dict(nnz=131072), False),
+    ("att", 256, 256, 64, dict(density=0.1), False),
+    ("bias", 72, 64, 72, dict(density=0.3), True),
+    ("n36", 37, 53, 36, dict(density=0.3), False),   # n % 4 == 0: the half4 dense loads of the fall-through config
+]
+
+
+def main_half(out_path):
+    from oracle.csr import even_rows
+    dev = torch.device("cuda:0")
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    g = {}
+    for name, m, k, n, kw, with_bias in SPMM_HALF:
+        a = even_rows(random_csr(m, k, seed=500 + len(g), values="pm1", **kw))
+        vals = a.values.astype(np.float16)
+        b = dense_operand((k, n), 600 + len(g), "pm1").astype(np.float16)
+        bias = dense_operand((m,), 700 + len(g), "pm1") if with_bias else None
+        out = ref_gpu.spmm_half(m, k, t(vals), t(a.row_indices), t(a.row_offsets), t(a.column_indices), t(b),
+                                bias=None if bias is None else t(bias))
+        p = f"spmmh_{name}_"
+        g[p + "shape"] = np.array([m, k, n], dtype=np.int32)
+        g[p + "values"], g[p + "row_indices"] = vals, a.row_indices
+        g[p + "row_offsets"], g[p + "column_indices"] = a.row_offsets, a.column_indices
+        g[p + "dense"], g[p + "out"] = b, out.cpu().numpy()
+        if bias is not None:
+            g[p + "bias"] = bias
+    torch.cuda.synchronize()
+    g["meta"] = np.array([torch.cuda.get_device_name(0), torch.__version__, torch.version.cuda or ""])
+    os.makedirs(os.path.dirname(os.path.abspath(out_path)), exist_ok=True)
+    np.savez_compressed(out_path, **g)
+    print("wrote", out_path, os.path.getsize(out_path), "bytes;", len(g), "arrays")
 
 
 def main(out_path):
@@ -98,4 +145,7 @@ def main(out_path):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "ref_b200.npz"))
+    if len(sys.argv) > 1 and sys.argv[1] == "--half":
+        main_half(sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out", "ref_b200_f16.npz"))
+    else:
+        main(sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "ref_b200.npz"))

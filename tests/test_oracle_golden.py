@@ -71,3 +71,31 @@ def test_oracle_transpose_matches_cusparse_bit_exactly(g):
         np.testing.assert_array_equal(rot, g[p + "row_offsets_t"], err_msg=c)
         np.testing.assert_array_equal(cit, g[p + "column_indices_t"], err_msg=c)
         np.testing.assert_array_equal(vt, g[p + "values_t"], err_msg=c)
+
+
+GOLDEN16 = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_b200_f16.npz")
+
+
+@pytest.mark.skipif(not os.path.exists(GOLDEN16), reason="fp16 golden vectors not generated yet")
+def test_oracle_matches_reference_half_spmm():
+    """ref_b200_f16.npz: sputnik::CudaSpmm(half2 ...) (cuda_spmm.cu.cc:511-570) on a B200.  The fp64
+    oracle on the same fp16 inputs must agree within one rounding of the result to fp16 plus the fp32
+    accumulation bound; and within the reference's own 5e-2 (spmm_test.cu.cc:207)."""
+    g16 = np.load(GOLDEN16)
+    assert "B200" in str(g16["meta"][0])
+    names = sorted({k.split("_")[1] for k in g16.files if k.startswith("spmmh_")})
+    assert len(names) >= 8
+    for c in names:
+        p = f"spmmh_{c}_"
+        m, k, n = g16[p + "shape"]
+        v32, d32 = g16[p + "values"].astype(np.float32), g16[p + "dense"].astype(np.float32)
+        bias = g16[p + "bias"] if p + "bias" in g16.files else None
+        assert np.all(np.diff(g16[p + "row_offsets"]) % 2 == 0)       # cuda_spmm.h:75-113
+        ref = oracle.spmm(m, k, v32, g16[p + "row_offsets"], g16[p + "column_indices"], d32, bias=bias,
+                          relu=bias is not None).astype(np.float64)
+        scale = oracle.spmm_abs(m, k, v32, g16[p + "row_offsets"], g16[p + "column_indices"], d32)
+        if bias is not None:
+            scale = scale + np.abs(bias)[:, None]
+        err = np.abs(ref - g16[p + "out"].astype(np.float64))
+        assert np.all(err <= 2.0 ** -10 * np.abs(ref) + 1e-5 * scale + 1e-30), (c, err.max())
+        assert err.max() < 5e-2

@@ -224,6 +224,26 @@ def c4(dev, flush, replicas):
     total = ms_sddmm + ms_soft + ms_spmm
     emit("C4", "attention fwd (3 ops)", total, r * (16 * nnz + 16 * s * d) + 2 * topo + 4 * (2 * s + 1),
          4.0 * nnz * d * r, {"replicas_per_gpu": r, "replicas_total": replicas})
+    # fp32 SpMM through the row-split kernel (variant 5) for an A/B against the gather kernel
+    ops.set_variant("spmm", 5)
+    ms_rs = timeit(lambda: ops.spmm(s, s, probs, ri, ro, ci, vv))
+    ops.set_variant("spmm", 0)
+    emit("C4", "spmm (row-split kernel, fp32)", ms_rs, r * (4 * nnz + 8 * s * d) + topo, 2.0 * nnz * d * r,
+         {"replicas_per_gpu": r, "gather_ms": round(ms_spmm, 4)})
+    # 16-bit storage, fp32 arithmetic: the same three ops (algorithmic bytes halve, topology stays int32)
+    for name, dt in (("f16", torch.float16), ("bf16", torch.bfloat16)):
+        qh, kh, vh = q.to(dt), kk.to(dt), vv.to(dt)
+        sc_h = ops.sddmm(s, s, ri, ro, ci, qh, kh)
+        ms_a = timeit(lambda: ops.sddmm(s, s, ri, ro, ci, qh, kh))
+        pr_h = ops.sparse_softmax_scaled(sc_h, ri, ro, ci, 0.125)
+        ms_b = timeit(lambda: ops.sparse_softmax_scaled(sc_h, ri, ro, ci, 0.125))
+        ms_c = timeit(lambda: ops.spmm(s, s, pr_h, ri, ro, ci, vh))
+        emit("C4", f"sddmm {name}", ms_a, r * (2 * nnz + 4 * s * d) + topo, 2.0 * nnz * d * r, {"replicas_per_gpu": r})
+        emit("C4", f"csr_softmax {name} (scale fused)", ms_b, r * 4 * nnz + 4 * (2 * s + 1), 5.0 * nnz * r, {"replicas_per_gpu": r})
+        emit("C4", f"spmm {name}", ms_c, r * (2 * nnz + 4 * s * d) + topo, 2.0 * nnz * d * r, {"replicas_per_gpu": r})
+        emit("C4", f"attention fwd (3 ops) {name}", ms_a + ms_b + ms_c, r * (8 * nnz + 8 * s * d) + 2 * topo + 4 * (2 * s + 1),
+             4.0 * nnz * d * r, {"replicas_per_gpu": r, "replicas_total": replicas, "fp32_chain_ms": round(total, 4)})
+        del qh, kh, vh, sc_h, pr_h
     for w in [int(x) for x in os.environ.get("TSP_ATTN_WARPS", "0").split(",")]:
         ops.set_variant("attn_warps", w)
         ms_fused = timeit(lambda: ops.sparse_attention(s, s, ri, ro, ci, q, kk, vv, 0.125))

@@ -16,6 +16,8 @@ SYMBOLS = (
     "tsp_launch_count",
     "tsp_plan_create", "tsp_plan_destroy", "tsp_plan_sorted", "tsp_plan_transpose", "tsp_plan_spmm_f32",
     "tsp_plan_sddmm_f32",
+    "tsp_spmm_f16", "tsp_spmm_bf16", "tsp_sddmm_f16", "tsp_sddmm_bf16", "tsp_csr_softmax_f16", "tsp_csr_softmax_bf16",
+    "tsp_permute_values_b16",
 )
 
 _lib = None
@@ -44,6 +46,13 @@ def load() -> ctypes.CDLL:
         lib.tsp_sparse_attention_f32.argtypes = [i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_set_variant.argtypes = [ctypes.c_char_p, i]
         lib.tsp_launch_count.restype = ctypes.c_ulonglong
+        for name in ("tsp_spmm_f16", "tsp_spmm_bf16"):
+            getattr(lib, name).argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, i, vp, vp]
+        for name in ("tsp_sddmm_f16", "tsp_sddmm_bf16"):
+            getattr(lib, name).argtypes = [i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
+        for name in ("tsp_csr_softmax_f16", "tsp_csr_softmax_bf16"):
+            getattr(lib, name).argtypes = [i, i, i, f, vp, vp, vp, vp, vp]
+        lib.tsp_permute_values_b16.argtypes = [i, i, vp, vp, vp, vp]
         pp = ctypes.POINTER(vp)
         lib.tsp_plan_create.argtypes = [i, i, i, vp, vp, vp, pp]
         lib.tsp_plan_destroy.argtypes = [vp]

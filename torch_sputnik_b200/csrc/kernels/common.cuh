@@ -233,38 +233,56 @@ __device__ __forceinline__ unsigned pack_pair<__nv_bfloat16>(float lo, float hi)
   return *reinterpret_cast<const unsigned*>(&h);
 }
 
-// E consecutive elements of T at p (aligned to E * sizeof(T)) -> fp32, one read-only vector load.
+// Raw register image of a vector load of BYTES bytes.
+template <int BYTES>
+struct RawVec;
+template <>
+struct RawVec<16> { using type = uint4; };
+template <>
+struct RawVec<8> { using type = uint2; };
+template <>
+struct RawVec<4> { using type = unsigned; };
+template <>
+struct RawVec<2> { using type = unsigned short; };
+
+// E consecutive elements of T at p (aligned to E * sizeof(T)): one read-only vector load, kept as
+// raw bits so that several loads can be in flight without holding their fp32 expansion.
 template <typename T, int E>
-__device__ __forceinline__ void load_elems(float (&dst)[E], const T* p) {
+__device__ __forceinline__ typename RawVec<E * sizeof(T)>::type ldg_raw(const T* p) {
+  return __ldg(reinterpret_cast<const typename RawVec<E * sizeof(T)>::type*>(p));
+}
+
+template <typename T, int E>
+__device__ __forceinline__ void unpack_raw(float (&dst)[E], const typename RawVec<E * sizeof(T)>::type& v) {
   if constexpr (sizeof(T) == 4) {
     static_assert(E == 1 || E == 2 || E == 4, "fp32: 1, 2 or 4 elements per load");
     if constexpr (E == 4) {
-      const float4 v = __ldg(reinterpret_cast<const float4*>(p));
-      dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+      dst[0] = __uint_as_float(v.x); dst[1] = __uint_as_float(v.y); dst[2] = __uint_as_float(v.z); dst[3] = __uint_as_float(v.w);
     } else if constexpr (E == 2) {
-      const float2 v = __ldg(reinterpret_cast<const float2*>(p));
-      dst[0] = v.x; dst[1] = v.y;
+      dst[0] = __uint_as_float(v.x); dst[1] = __uint_as_float(v.y);
     } else {
-      dst[0] = __ldg(reinterpret_cast<const float*>(p));
+      dst[0] = __uint_as_float(v);
     }
   } else {
     static_assert(E == 1 || E == 2 || E == 4 || E == 8, "16-bit: 1, 2, 4 or 8 elements per load");
     if constexpr (E == 8) {
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
       const float2 a = unpack_pair<T>(v.x), b = unpack_pair<T>(v.y), c = unpack_pair<T>(v.z), d = unpack_pair<T>(v.w);
       dst[0] = a.x; dst[1] = a.y; dst[2] = b.x; dst[3] = b.y; dst[4] = c.x; dst[5] = c.y; dst[6] = d.x; dst[7] = d.y;
     } else if constexpr (E == 4) {
-      const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
       const float2 a = unpack_pair<T>(v.x), b = unpack_pair<T>(v.y);
       dst[0] = a.x; dst[1] = a.y; dst[2] = b.x; dst[3] = b.y;
     } else if constexpr (E == 2) {
-      const float2 a = unpack_pair<T>(__ldg(reinterpret_cast<const unsigned*>(p)));
+      const float2 a = unpack_pair<T>(v);
       dst[0] = a.x; dst[1] = a.y;
     } else {
-      const unsigned short raw = __ldg(reinterpret_cast<const unsigned short*>(p));
-      dst[0] = unpack_pair<T>((unsigned)raw).x;
+      dst[0] = unpack_pair<T>((unsigned)v).x;
     }
   }
+}
+
+template <typename T, int E>
+__device__ __forceinline__ void load_elems(float (&dst)[E], const T* p) {
+  unpack_raw<T, E>(dst, ldg_raw<T, E>(p));
 }
 
 // fp32 -> E consecutive elements of T at p (round to nearest even), one vector store.

@@ -12,18 +12,32 @@
 
 namespace tsp {
 
-struct SoftmaxArgs {
+// T: storage type of the values (float, __half, __nv_bfloat16); max / exp / sum are fp32.
+template <typename T>
+struct SoftmaxArgsT {
   int m, nnz;
   float scale;
   const int* row_indices;  // may be null
   const int* row_offsets;
-  const float* x;   // forward: values; backward: y
-  const float* dy;  // backward only
-  float* out;
+  const T* x;   // forward: values; backward: y
+  const T* dy;  // backward only
+  T* out;
 };
+using SoftmaxArgs = SoftmaxArgsT<float>;
 
-template <int REG, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxArgs a) {
+template <typename T>
+__device__ __forceinline__ float ld_once(const T* p) {
+  if constexpr (sizeof(T) == 4) return ld_stream_f(reinterpret_cast<const float*>(p));
+  else return Elem<T>::to_f(*p);
+}
+template <typename T>
+__device__ __forceinline__ void st_once(T* p, float v) {
+  if constexpr (sizeof(T) == 4) st_stream_f(reinterpret_cast<float*>(p), v);
+  else *p = Elem<T>::from_f(v);
+}
+
+template <int REG, int WARPS, typename T = float>
+__global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxArgsT<T> a) {
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int item = blockIdx.x * WARPS + warp;
@@ -33,8 +47,8 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
   const int len = __ldg(a.row_offsets + row + 1) - beg;
   if (len <= 0) return;
   const size_t base = (size_t)blockIdx.y * a.nnz + beg;
-  const float* __restrict__ in = a.x + base;
-  float* __restrict__ out = a.out + base;
+  const T* __restrict__ in = a.x + base;
+  T* __restrict__ out = a.out + base;
   const float scale = a.scale;
 
   if (len <= 32 * REG) {
@@ -43,7 +57,7 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
 #pragma unroll
     for (int i = 0; i < REG; ++i) {
       const int idx = lane + 32 * i;
-      v[i] = idx < len ? ld_stream_f(in + idx) * scale : -INFINITY;
+      v[i] = idx < len ? ld_once(in + idx) * scale : -INFINITY;
       mx = fmaxf(mx, v[i]);
     }
     mx = warp_max(mx);
@@ -60,18 +74,18 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
 #pragma unroll
     for (int i = 0; i < REG; ++i) {
       const int idx = lane + 32 * i;
-      if (idx < len) st_stream_f(out + idx, v[i] * inv);
+      if (idx < len) st_once(out + idx, v[i] * inv);
     }
   } else {
     float mx = -INFINITY;
-    for (int idx = lane; idx < len; idx += 32) mx = fmaxf(mx, __ldg(in + idx) * scale);
+    for (int idx = lane; idx < len; idx += 32) mx = fmaxf(mx, Elem<T>::to_f(in[idx]) * scale);
     mx = warp_max(mx);
     float sum = 0.f;
-    for (int idx = lane; idx < len; idx += 32) sum += expf(__ldg(in + idx) * scale - mx);
+    for (int idx = lane; idx < len; idx += 32) sum += expf(Elem<T>::to_f(in[idx]) * scale - mx);
     sum = warp_sum(sum);
     const float inv = 1.0f / sum;
     for (int idx = lane; idx < len; idx += 32)
-      out[idx] = expf(__ldg(in + idx) * scale - mx) * inv;
+      out[idx] = Elem<T>::from_f(expf(Elem<T>::to_f(in[idx]) * scale - mx) * inv);
   }
 }
 

@@ -186,9 +186,11 @@ __global__ void __launch_bounds__(256) transpose_finish_kernel(const TransposeFi
     a.values_t[(size_t)r * a.nnz + p] = __ldg(a.values + (size_t)r * a.nnz + src);
 }
 
+// V: float, or unsigned short for any 16-bit storage type (a pure move).
+template <typename V>
 __global__ void __launch_bounds__(256)
-permute_values_kernel(int nnz, const float* __restrict__ values, const int* __restrict__ perm,
-                      float* __restrict__ values_t) {
+permute_values_kernel(int nnz, const V* __restrict__ values, const int* __restrict__ perm,
+                      V* __restrict__ values_t) {
   const int p = blockIdx.x * 256 + threadIdx.x;
   if (p >= nnz) return;
   const size_t base = (size_t)blockIdx.y * nnz;

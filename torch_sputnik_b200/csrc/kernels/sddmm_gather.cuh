@@ -17,13 +17,15 @@
 
 namespace tsp {
 
-struct SddmmArgs {
+// T: storage type of lhs / rhs / out (float, __half, __nv_bfloat16); arithmetic is fp32.
+template <typename T>
+struct SddmmArgsT {
   int m, k, n, nnz;
   const int* row_offsets;
   const int* column_indices;
-  const float* lhs;  // [replicas, m, k]
-  const float* rhs;  // [replicas, n, k]
-  float* out;        // [replicas, nnz]
+  const T* lhs;  // [replicas, m, k]
+  const T* rhs;  // [replicas, n, k]
+  T* out;        // [replicas, nnz]
   // guard_flag != null: this launch is the unsorted-columns fallback of a staged launch and runs
   // only if *guard_flag != 0 (see StagedGuard, spmm_gather.cuh).
   const unsigned* guard_flag = nullptr;
@@ -32,6 +34,7 @@ struct SddmmArgs {
   // their k loop, grid.y is 1.
   int reduce_reps = 0;
 };
+using SddmmArgs = SddmmArgsT<float>;
 
 // Row containing flat nonzero j: largest i with row_offsets[i] <= j (skips empty rows).
 __device__ __forceinline__ int row_of_nonzero(const int* __restrict__ row_offsets, int m, int j) {
@@ -59,8 +62,8 @@ __device__ __forceinline__ void transpose_reduce(float (&vals)[LPN], int lane) {
   }
 }
 
-template <int VEC, int LPN, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArgs a) {
+template <int VEC, int LPN, int WARPS, typename T = float>
+__global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArgsT<T> a) {
   constexpr int G = 32 / LPN;  // nonzeros processed side by side in a warp
   constexpr int NPG = LPN;     // nonzeros per group per chunk (G * NPG == 32)
   constexpr int KSTEP = LPN * VEC;
@@ -95,8 +98,8 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
 
   // Group g owns nonzeros j0 + g*NPG + i, i in [0, NPG).
   for (int rr = 0; rr < nrep; ++rr) {
-  const float* __restrict__ lhs = a.lhs + (size_t)(rep + rr) * a.m * k;
-  const float* __restrict__ rhs = a.rhs + (size_t)(rep + rr) * a.n * k;
+  const T* __restrict__ lhs = a.lhs + (size_t)(rep + rr) * a.m * k;
+  const T* __restrict__ rhs = a.rhs + (size_t)(rep + rr) * a.n * k;
   for (int kk = 0; kk < k; kk += KSTEP) {
     const int kofs = kk + sub * VEC;
     const bool kin = kofs < k;  // VEC == 4 implies k % 4 == 0, so a vector is all-in or all-out
@@ -109,25 +112,13 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
       const int c = __shfl_sync(kFullMask, my_col, src);
       if (kin && (j0 + src) < a.nnz) {
         if (r != prev_row) {
-#pragma unroll
-          for (int v = 0; v < VEC; ++v) av[v] = 0.f;
-          if constexpr (VEC == 4) {
-            const float4 t = ldg_f4(lhs + (size_t)r * k + kofs);
-            av[0] = t.x; av[1] = t.y; av[2] = t.z; av[3] = t.w;
-          } else {
-            av[0] = __ldg(lhs + (size_t)r * k + kofs);
-          }
+          load_elems<T, VEC>(av, lhs + (size_t)r * k + kofs);
           prev_row = r;
         }
-        if constexpr (VEC == 4) {
-          const float4 b = ldg_f4(rhs + (size_t)c * k + kofs);
-          acc[i] = fmaf(av[0], b.x, acc[i]);
-          acc[i] = fmaf(av[1], b.y, acc[i]);
-          acc[i] = fmaf(av[2], b.z, acc[i]);
-          acc[i] = fmaf(av[3], b.w, acc[i]);
-        } else {
-          acc[i] = fmaf(av[0], __ldg(rhs + (size_t)c * k + kofs), acc[i]);
-        }
+        float b[VEC];
+        load_elems<T, VEC>(b, rhs + (size_t)c * k + kofs);
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[i] = fmaf(av[v], b[v], acc[i]);
       }
     }
   }
@@ -135,7 +126,7 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
 
   transpose_reduce<LPN>(acc, lane);
   const int j = j0 + grp * NPG + sub;
-  if (j < a.nnz) a.out[(size_t)rep * a.nnz + j] = acc[0];
+  if (j < a.nnz) a.out[(size_t)rep * a.nnz + j] = Elem<T>::from_f(acc[0]);
 }
 
 // out[j] = sum_r scratch[r, j] (ascending r).
@@ -148,11 +139,11 @@ reduce_replicas_kernel(const float* __restrict__ scratch, int nnz, int replicas,
   out[j] = s;
 }
 
-template <int VEC, int LPN>
-inline void launch_sddmm_gather(const SddmmArgs& a, int replicas, cudaStream_t stream) {
+template <int VEC, int LPN, typename T = float>
+inline void launch_sddmm_gather(const SddmmArgsT<T>& a, int replicas, cudaStream_t stream) {
   constexpr int WARPS = 4;
   dim3 grid(ceil_div(ceil_div(a.nnz, 32), WARPS), a.reduce_reps > 0 ? 1 : replicas, 1);
-  sddmm_gather_kernel<VEC, LPN, WARPS><<<grid, WARPS * 32, 0, stream>>>(a);
+  sddmm_gather_kernel<VEC, LPN, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a);
 }
 
 }  // namespace tsp

@@ -22,14 +22,20 @@
 // lanes -- the shape of the reference's (all_reduce.h:61-80), a different association.
 // Works for any column order (no sortedness assumption).  Needs k % 32 == 0, k <= 128,
 // 16-byte aligned operands and n * k * 4 < 2^31.
+// 16-bit storage (T = __half / __nv_bfloat16, fp32 products and sums, result rounded once): the
+// same kernel with 8 elements per 16-byte chunk -- k % 64 == 0, k <= 256; a k = 64 row is ONE
+// 128-byte request, half the L1 wavefronts per FMA of the fp32 layout.
 #pragma once
 #include "sddmm_gather.cuh"
 
 namespace tsp {
 
-template <int KC, int WARPS>   // k = 32 * KC
-__global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgs a) {
-  constexpr int K = 32 * KC;
+// T = storage type; a quarter-warp reads 128 bytes of a row per step = 8 lanes x E elements
+// (E = 4 fp32 / 8 fp16 or bf16), so k = 8 * E * KC: 16-bit operands need half the steps per nonzero.
+template <int KC, int WARPS, typename T = float>
+__global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT<T> a) {
+  constexpr int E = Elem<T>::kPer16;
+  constexpr int K = 8 * E * KC;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * WARPS + warp;
   if (row >= a.m) return;
@@ -39,83 +45,77 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgs 
   const int beg = __ldg(a.row_offsets + row), end = __ldg(a.row_offsets + row + 1);
   if (beg >= end) return;
   const int* __restrict__ cols = a.column_indices;
-  float* __restrict__ out = a.out + (size_t)rep * a.nnz;
-  // this lane's chunk `sub` of rhs row 0 (float4 units); chunk cc of row c is at + c * (K/4) + cc * 8
-  const float4* const rbase = reinterpret_cast<const float4*>(a.rhs + (size_t)rep * a.n * K) + sub;
-  const float4* const lrow = reinterpret_cast<const float4*>(a.lhs + ((size_t)rep * a.m + row) * K) + sub;
-  float4 lv[KC];
+  T* __restrict__ out = a.out + (size_t)rep * a.nnz;
+  // this lane's chunk `sub` of rhs row 0 (16-byte units); chunk cc of row c is at + c * (8 * KC) + cc * 8
+  const T* const rbase = a.rhs + (size_t)rep * a.n * K + sub * E;
+  const T* const lrow = a.lhs + ((size_t)rep * a.m + row) * K + sub * E;
+  float lv[KC][E];
 #pragma unroll
-  for (int cc = 0; cc < KC; ++cc) lv[cc] = __ldg(lrow + cc * 8);
+  for (int cc = 0; cc < KC; ++cc) load_elems<T, E>(lv[cc], lrow + cc * 8 * E);
+  auto dot_row = [&](const unsigned o) {   // o: rhs row offset in 16-byte units
+    float s = 0.f;
+#pragma unroll
+    for (int cc = 0; cc < KC; ++cc) {
+      float x[E];
+      load_elems<T, E>(x, rbase + ((size_t)o + cc * 8) * E);
+#pragma unroll
+      for (int e = 0; e < E; ++e) s = fmaf(lv[cc][e], x[e], s);
+    }
+    return s;
+  };
 
   for (int p = beg; p < end; p += 32) {
     const int cnt = min(32, end - p);
     // rhs row offset of nonzero p + lane in float4 units (row 0 for the lanes past the row's end:
     // a valid address, the result is never stored)
-    const unsigned myoff = lane < cnt ? (unsigned)__ldg(cols + p + lane) * (unsigned)(K / 4) : 0u;
+    const unsigned myoff = lane < cnt ? (unsigned)__ldg(cols + p + lane) * (unsigned)(8 * KC) : 0u;
     float acc[8];
     if (cnt == 32) {
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
-        const unsigned o = __shfl_sync(kFullMask, myoff, 4 * g + q);
-        float s = 0.f;
-#pragma unroll
-        for (int cc = 0; cc < KC; ++cc) {
-          const float4 x = __ldg(rbase + o + cc * 8);
-          s = fmaf(lv[cc].x, x.x, s);
-          s = fmaf(lv[cc].y, x.y, s);
-          s = fmaf(lv[cc].z, x.z, s);
-          s = fmaf(lv[cc].w, x.w, s);
-        }
-        acc[g] = s;
+        acc[g] = dot_row(__shfl_sync(kFullMask, myoff, 4 * g + q));
       }
     } else {
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
         acc[g] = 0.f;
         if (4 * g < cnt) {   // warp-uniform
-          const unsigned o = __shfl_sync(kFullMask, myoff, 4 * g + q);
-          float s = 0.f;
-#pragma unroll
-          for (int cc = 0; cc < KC; ++cc) {
-            const float4 x = __ldg(rbase + o + cc * 8);
-            s = fmaf(lv[cc].x, x.x, s);
-            s = fmaf(lv[cc].y, x.y, s);
-            s = fmaf(lv[cc].z, x.z, s);
-            s = fmaf(lv[cc].w, x.w, s);
-          }
-          acc[g] = s;
+          acc[g] = dot_row(__shfl_sync(kFullMask, myoff, 4 * g + q));
         }
       }
     }
     transpose_reduce<8>(acc, sub);   // lane (q, sub) now holds nonzero 4 * sub + q of the batch
     const int j = 4 * sub + q;
-    if (j < cnt) out[p + j] = acc[0];
+    if (j < cnt) out[p + j] = Elem<T>::from_f(acc[0]);
   }
 }
 
-inline bool sddmm_rows_applicable(const SddmmArgs& a) {
-  if (a.k % 32 != 0 || a.k > 128 || a.k < 32) return false;
+template <typename T>
+inline bool sddmm_rows_applicable(const SddmmArgsT<T>& a) {
+  constexpr int chunk = 8 * Elem<T>::kPer16;   // elements per quarter-warp step: 32 fp32 / 64 16-bit
+  if (a.k % chunk != 0 || a.k > 4 * chunk || a.k < chunk) return false;
   if (!aligned16(a.lhs) || !aligned16(a.rhs)) return false;
-  return (unsigned long long)a.n * (unsigned long long)a.k * 4ull < (1ull << 31);
+  return (unsigned long long)a.n * (unsigned long long)a.k * sizeof(T) < (1ull << 31);
 }
 
 extern std::atomic<int> g_sddmm_warps;   // benchmark knob "sddmm_warps": rows per CTA (0 = default 16)
 
-template <int KC>
-inline void launch_sddmm_rows_kc(const SddmmArgs& a, int replicas, cudaStream_t stream) {
+template <int KC, typename T>
+inline void launch_sddmm_rows_kc(const SddmmArgsT<T>& a, int replicas, cudaStream_t stream) {
   const int w = g_sddmm_warps.load();
-  if (w == 4) sddmm_rows_kernel<KC, 4><<<dim3(ceil_div(a.m, 4), replicas), 128, 0, stream>>>(a);
-  else if (w == 8) sddmm_rows_kernel<KC, 8><<<dim3(ceil_div(a.m, 8), replicas), 256, 0, stream>>>(a);
-  else if (w == 32) sddmm_rows_kernel<KC, 32><<<dim3(ceil_div(a.m, 32), replicas), 1024, 0, stream>>>(a);
-  else sddmm_rows_kernel<KC, 16><<<dim3(ceil_div(a.m, 16), replicas), 512, 0, stream>>>(a);
+  if (w == 4) sddmm_rows_kernel<KC, 4, T><<<dim3(ceil_div(a.m, 4), replicas), 128, 0, stream>>>(a);
+  else if (w == 8) sddmm_rows_kernel<KC, 8, T><<<dim3(ceil_div(a.m, 8), replicas), 256, 0, stream>>>(a);
+  else if (w == 32) sddmm_rows_kernel<KC, 32, T><<<dim3(ceil_div(a.m, 32), replicas), 1024, 0, stream>>>(a);
+  else sddmm_rows_kernel<KC, 16, T><<<dim3(ceil_div(a.m, 16), replicas), 512, 0, stream>>>(a);
 }
 
-inline void launch_sddmm_rows(const SddmmArgs& a, int replicas, cudaStream_t stream) {
-  switch (a.k / 32) {
-    case 1: launch_sddmm_rows_kc<1>(a, replicas, stream); break;
-    case 2: launch_sddmm_rows_kc<2>(a, replicas, stream); break;
-    case 3: launch_sddmm_rows_kc<3>(a, replicas, stream); break;
-    default: launch_sddmm_rows_kc<4>(a, replicas, stream); break;
+template <typename T>
+inline void launch_sddmm_rows(const SddmmArgsT<T>& a, int replicas, cudaStream_t stream) {
+  switch (a.k / (8 * Elem<T>::kPer16)) {
+    case 1: launch_sddmm_rows_kc<1, T>(a, replicas, stream); break;
+    case 2: launch_sddmm_rows_kc<2, T>(a, replicas, stream); break;
+    case 3: launch_sddmm_rows_kc<3, T>(a, replicas, stream); break;
+    default: launch_sddmm_rows_kc<4, T>(a, replicas, stream); break;
   }
 }
 

@@ -63,7 +63,8 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArg
 #pragma unroll
     for (int g0 = 0; g0 < LPN; g0 += UNR) {
       if (g0 * G >= cnt) break;   // warp-uniform
-      float v[UNR], b[UNR][EPL];
+      float v[UNR];
+      typename RawVec<EPL * sizeof(T)>::type raw[UNR];
       bool on[UNR];
 #pragma unroll
       for (int u = 0; u < UNR; ++u) {
@@ -71,13 +72,15 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArg
         v[u] = __shfl_sync(kFullMask, myval, src);
         const unsigned o = __shfl_sync(kFullMask, myoff, src);
         on[u] = src < cnt && col_ok;
-        if (on[u]) load_elems<T, EPL>(b[u], lane_base + (size_t)o * EPL);
+        if (on[u]) raw[u] = ldg_raw<T, EPL>(lane_base + (size_t)o * EPL);
       }
 #pragma unroll
       for (int u = 0; u < UNR; ++u)
         if (on[u]) {
+          float b[EPL];
+          unpack_raw<T, EPL>(b, raw[u]);
 #pragma unroll
-          for (int e = 0; e < EPL; ++e) acc[e] = fmaf(v[u], b[u][e], acc[e]);
+          for (int e = 0; e < EPL; ++e) acc[e] = fmaf(v[u], b[e], acc[e]);
         }
     }
   }

@@ -64,6 +64,15 @@ torch::Tensor as_i32_indices(const torch::Tensor& t, const char* name) {
   return t.contiguous();
 }
 
+// fp32, or 16-bit storage (fp16 / bf16: the a13 entry points of include/tsp.h), made contiguous.
+torch::Tensor value_operand(const torch::Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda(), "torch_sputnik: ", name, " must be a CUDA tensor");
+  const auto st = t.scalar_type();
+  TORCH_CHECK(st == torch::kFloat32 || st == torch::kFloat16 || st == torch::kBFloat16, "torch_sputnik: ", name,
+              " must be float32, float16 or bfloat16, got ", st);
+  return t.contiguous();
+}
+
 void* current_stream() { return static_cast<void*>(at::cuda::getCurrentCUDAStream().stream()); }
 
 bool current_stream_capturing() {
@@ -241,8 +250,11 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values_in,
               ": values must have 1 or 2 dimensions");
   TORCH_CHECK(dense_in.dim() == 2 || dense_in.dim() == 3, "torch_sputnik.", op,
               ": dense must have 2 or 3 dimensions");
-  torch::Tensor values = f32_operand(values_in, "values");
-  torch::Tensor dense = f32_operand(dense_in, "dense");
+  torch::Tensor values = value_operand(values_in, "values");
+  torch::Tensor dense = value_operand(dense_in, "dense");
+  TORCH_CHECK(values.scalar_type() == dense.scalar_type(), "torch_sputnik.", op, ": values (", values.scalar_type(),
+              ") and dense (", dense.scalar_type(), ") must have the same dtype");
+  const auto dtype = values.scalar_type();
   c10::cuda::CUDAGuard guard(values.device());
   torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
   check_topology(m, row_indices, row_offsets, column_indices);
@@ -279,11 +291,20 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values_in,
     perm_ptr = perm_t.data_ptr<int>();
   }
 
-  auto options = torch::TensorOptions().dtype(torch::kFloat32).device(values.device());
+  auto options = torch::TensorOptions().dtype(dtype).device(values.device());
   // Reference quirk: `spmm` returns 2-D whenever the replica count is 1 (src/spmm_cuda.cu:46);
   // `left_spmm` is always 3-D (src/left_replicated_spmm.cu:30).
   torch::Tensor out = (left || replicas != 1) ? torch::empty({replicas, m, n}, options)
                                               : torch::empty({m, n}, options);
+  if (dtype != torch::kFloat32) {
+    // 16-bit storage, fp32 arithmetic, result in the storage type (cuda_spmm.h:75-127)
+    auto fn = dtype == torch::kFloat16 ? tsp_spmm_f16 : tsp_spmm_bf16;
+    check_rc(fn((int)m, (int)k, (int)n, (int)nnz, (int)replicas, shared ? 1 : 0, row_indices.data_ptr<int>(),
+                values.data_ptr(), perm_ptr, row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                dense.data_ptr(), bias_ptr, relu ? 1 : 0, out.data_ptr(), current_stream()),
+             op);
+    return out;
+  }
   if (auto e = get_plan(m, k, row_offsets, column_indices)) {
     check_rc(tsp_plan_spmm_f32(e->plan, (int)n, (int)replicas, shared ? 1 : 0, row_indices.data_ptr<int>(),
                                values.data_ptr<float>(), perm_ptr, dense.data_ptr<float>(), bias_ptr,
@@ -331,8 +352,12 @@ static torch::Tensor sddmm_impl(int m, int n, const torch::Tensor& row_indices_i
                                 const torch::Tensor& lhs_in, const torch::Tensor& rhs_in, bool reduce) {
   TORCH_CHECK(lhs_in.dim() == 2 || lhs_in.dim() == 3, "torch_sputnik.sddmm: lhs must be 2-D or 3-D");
   TORCH_CHECK(lhs_in.dim() == rhs_in.dim(), "torch_sputnik.sddmm: lhs and rhs must have the same rank");
-  torch::Tensor lhs = f32_operand(lhs_in, "lhs_matrix");
-  torch::Tensor rhs = f32_operand(rhs_in, "rhs_matrix");
+  torch::Tensor lhs = value_operand(lhs_in, "lhs_matrix");
+  torch::Tensor rhs = value_operand(rhs_in, "rhs_matrix");
+  TORCH_CHECK(lhs.scalar_type() == rhs.scalar_type(), "torch_sputnik.sddmm: lhs (", lhs.scalar_type(), ") and rhs (",
+              rhs.scalar_type(), ") must have the same dtype");
+  const auto dtype = lhs.scalar_type();
+  TORCH_CHECK(!reduce || dtype == torch::kFloat32, "torch_sputnik.sddmm_reduce: float32 only");
   c10::cuda::CUDAGuard guard(lhs.device());
   torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
   check_topology(m, row_indices, row_offsets, column_indices);
@@ -347,10 +372,17 @@ static torch::Tensor sddmm_impl(int m, int n, const torch::Tensor& row_indices_i
   TORCH_CHECK(dim_offset == 0 || rhs.size(0) == replicas,
               "torch_sputnik.sddmm: first dims of lhs and rhs must match");
 
-  auto options = torch::TensorOptions().dtype(torch::kFloat32).device(lhs.device());
+  auto options = torch::TensorOptions().dtype(dtype).device(lhs.device());
   torch::Tensor out = (replicas == 1 || reduce) ? torch::empty({nnz}, options)
                                                 : torch::empty({replicas, nnz}, options);
   const char* op = reduce ? "sddmm_reduce" : "sddmm";
+  if (dtype != torch::kFloat32) {
+    auto fn16 = dtype == torch::kFloat16 ? tsp_sddmm_f16 : tsp_sddmm_bf16;
+    check_rc(fn16(m, (int)k, n, (int)nnz, (int)replicas, row_indices.data_ptr<int>(), row_offsets.data_ptr<int>(),
+                  column_indices.data_ptr<int>(), lhs.data_ptr(), rhs.data_ptr(), out.data_ptr(), current_stream()),
+             op);
+    return out;
+  }
   if (auto e = get_plan(m, n, row_offsets, column_indices)) {
     check_rc(tsp_plan_sddmm_f32(e->plan, (int)k, (int)replicas, reduce ? 1 : 0, row_indices.data_ptr<int>(),
                                 lhs.data_ptr<float>(), rhs.data_ptr<float>(), out.data_ptr<float>(),
@@ -379,12 +411,12 @@ torch::Tensor sddmm_reduce(int m, int n, torch::Tensor row_indices, torch::Tenso
   return sddmm_impl(m, n, row_indices, row_offsets, column_indices, lhs, rhs, true);
 }
 
-static torch::Tensor softmax_impl(const torch::Tensor& values, const torch::Tensor& row_indices_in,
+static torch::Tensor softmax_impl(const torch::Tensor& values_in, const torch::Tensor& row_indices_in,
                                   const torch::Tensor& row_offsets,
                                   const torch::Tensor& column_indices, double scale) {
-  TORCH_CHECK(values.dim() == 1 || values.dim() == 2,
+  TORCH_CHECK(values_in.dim() == 1 || values_in.dim() == 2,
               "torch_sputnik.sparse_softmax: values must have 1 or 2 dimensions");
-  TSP_CHECK_CUDA_F32(values, "values");
+  torch::Tensor values = value_operand(values_in, "values");
   c10::cuda::CUDAGuard guard(values.device());
   torch::Tensor row_indices = as_i32_indices(row_indices_in, "row_indices");
   const int64_t m = row_indices.size(0);
@@ -394,6 +426,13 @@ static torch::Tensor softmax_impl(const torch::Tensor& values, const torch::Tens
               "torch_sputnik.sparse_softmax: number of values must equal number of column indices");
   const int64_t replicas = values.dim() == 2 ? values.size(0) : 1;
   torch::Tensor out = torch::empty_like(values);
+  if (values.scalar_type() != torch::kFloat32) {
+    auto fn16 = values.scalar_type() == torch::kFloat16 ? tsp_csr_softmax_f16 : tsp_csr_softmax_bf16;
+    check_rc(fn16((int)m, (int)nnz, (int)replicas, (float)scale, values.data_ptr(), row_indices.data_ptr<int>(),
+                  row_offsets.data_ptr<int>(), out.data_ptr(), current_stream()),
+             "sparse_softmax");
+    return out;
+  }
   check_rc(tsp_csr_softmax_f32((int)m, (int)nnz, (int)replicas, (float)scale,
                                values.data_ptr<float>(), row_indices.data_ptr<int>(),
                                row_offsets.data_ptr<int>(), out.data_ptr<float>(), current_stream()),
@@ -439,10 +478,15 @@ torch::Tensor sparse_softmax_backward(torch::Tensor y, torch::Tensor dy, torch::
 
 static torch::Tensor permute_values_impl(const torch::Tensor& values, const torch::Tensor& perm) {
   torch::Tensor out = torch::empty_like(values);
-  check_rc(tsp_permute_values_f32((int)perm.size(0), values.dim() == 2 ? (int)values.size(0) : 1,
-                                  values.data_ptr<float>(), perm.data_ptr<int>(),
-                                  out.data_ptr<float>(), current_stream()),
-           "permute_values");
+  const int replicas = values.dim() == 2 ? (int)values.size(0) : 1;
+  if (values.scalar_type() != torch::kFloat32)
+    check_rc(tsp_permute_values_b16((int)perm.size(0), replicas, values.data_ptr(), perm.data_ptr<int>(), out.data_ptr(),
+                                    current_stream()),
+             "permute_values");
+  else
+    check_rc(tsp_permute_values_f32((int)perm.size(0), replicas, values.data_ptr<float>(), perm.data_ptr<int>(),
+                                    out.data_ptr<float>(), current_stream()),
+             "permute_values");
   return out;
 }
 
@@ -455,7 +499,7 @@ static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tens
   // replica by replica with the shared topology.
   TORCH_CHECK(values_in.dim() == 1 || values_in.dim() == 2,
               "torch_sputnik.csr_transpose: values must have 1 or 2 dimensions");
-  torch::Tensor values = f32_operand(values_in, "values");
+  torch::Tensor values = value_operand(values_in, "values");
   TSP_CHECK_CUDA_I32(row_offsets, "row_offsets");
   TSP_CHECK_CUDA_I32(column_indices, "column_indices");
   TORCH_CHECK(row_offsets.dim() == 1 && row_offsets.size(0) == m + 1,
@@ -480,6 +524,22 @@ static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tens
   }
 
   auto iopt = torch::TensorOptions().dtype(torch::kInt32).device(values.device());
+  if (values.scalar_type() != torch::kFloat32) {
+    // 16-bit values, unplanned: sort the topology alone, then move the values through the permutation
+    torch::Tensor row_offsets_t = torch::empty({n + 1}, iopt);
+    torch::Tensor column_indices_t = torch::empty({nnz}, iopt);
+    torch::Tensor perm = torch::empty({nnz}, iopt);
+    const size_t wsb = tsp_csr_transpose_workspace(m, n, (int)nnz);
+    torch::Tensor ws = torch::empty({(int64_t)wsb + 256}, torch::TensorOptions().dtype(torch::kUInt8).device(values.device()));
+    check_rc(tsp_csr_transpose_f32(m, n, (int)nnz, 0, nullptr, row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                                   nullptr, row_offsets_t.data_ptr<int>(), column_indices_t.data_ptr<int>(),
+                                   perm.data_ptr<int>(), ws.data_ptr(), wsb + 256, current_stream()),
+             "csr_transpose");
+    std::vector<torch::Tensor> out{nnz > 0 ? permute_values_impl(values, perm) : torch::empty_like(values), row_offsets_t,
+                                   column_indices_t};
+    if (want_perm) out.push_back(perm);
+    return out;
+  }
   torch::Tensor values_t = torch::empty_like(values);
   torch::Tensor row_offsets_t = torch::empty({n + 1}, iopt);
   torch::Tensor column_indices_t = torch::empty({nnz}, iopt);
@@ -533,8 +593,8 @@ std::vector<torch::Tensor> csr_transpose_with_perm(int m, int n, torch::Tensor v
   return transpose_impl(m, n, values, row_offsets, column_indices, true);
 }
 
-torch::Tensor permute_values(torch::Tensor values, torch::Tensor perm) {
-  TSP_CHECK_CUDA_F32(values, "values");
+torch::Tensor permute_values(torch::Tensor values_in, torch::Tensor perm) {
+  torch::Tensor values = value_operand(values_in, "values");
   TSP_CHECK_CUDA_I32(perm, "perm");
   TORCH_CHECK(values.dim() == 1 || values.dim() == 2, "torch_sputnik.permute_values: values must be 1-D or 2-D");
   TORCH_CHECK(perm.dim() == 1 && perm.size(0) == values.size(-1),

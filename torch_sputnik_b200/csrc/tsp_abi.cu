@@ -13,6 +13,7 @@
 #include "kernels/sddmm_gather.cuh"
 #include "kernels/spmm_gather.cuh"
 #include "kernels/spmm_staged.cuh"
+#include "kernels/spmm_rowsplit.cuh"
 #include "kernels/sddmm_sampled.cuh"
 #include "kernels/sddmm_rows.cuh"
 #include "kernels/attention_rows.cuh"
@@ -27,6 +28,7 @@ std::atomic<int> g_spmm_warps{0};
 std::atomic<int> g_sddmm_warps{0};
 std::atomic<int> g_attn_warps{0};
 static std::atomic<int> g_sddmm_variant{0};
+static std::atomic<int> g_spmm_rowsplit_max_n{0};   // fp32 operands up to this many columns take spmm_rowsplit
 static std::atomic<int> g_sddmm_bn{0};
 static std::atomic<int> g_sddmm_p{0};
 
@@ -72,6 +74,7 @@ unsigned long long tsp_launch_count(void) { return g_launches.load(); }
 
 int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm") == 0) return g_spmm_variant.exchange(variant);
+  if (op && strcmp(op, "spmm_rowsplit_max_n") == 0) return g_spmm_rowsplit_max_n.exchange(variant);
   if (op && strcmp(op, "spmm_warps") == 0) return g_spmm_warps.exchange(variant);
   if (op && strcmp(op, "sddmm_warps") == 0) return g_sddmm_warps.exchange(variant);
   if (op && strcmp(op, "attn_warps") == 0) return g_attn_warps.exchange(variant);
@@ -220,6 +223,13 @@ static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, con
       TSP_CHECK_LAUNCH("tsp_spmm_f32 (gather fallback)");
       return TSP_OK;
     }
+  }
+  // variant 5 (and the heuristic for narrow 16-byte-aligned operands): the row-split kernel, whose
+  // G groups of lanes take G nonzeros at once instead of leaving 32 - n/4 lanes idle.
+  if ((variant == 5 || (variant == 0 && g_spmm_rowsplit_max_n.load() >= n && vec4_ok)) && spmm_rowsplit_applicable(a)) {
+    launch_spmm_rowsplit<float>(a, replicas, stream);
+    TSP_CHECK_LAUNCH("tsp_spmm_f32 (rowsplit)");
+    return TSP_OK;
   }
   if (vec4_ok && n > 128) {
     launch_spmm_gather<4, 2>(a, replicas, stream);
@@ -425,29 +435,39 @@ static int pick_softmax_reg(int m, int nnz) {
   return 32;
 }
 
-int tsp_csr_softmax_f32(int m, int nnz, int replicas, float scale, const float* values,
-                        const int* row_indices, const int* row_offsets, float* out,
-                        void* stream_) {
+}  // extern "C"
+
+template <typename T>
+static int softmax_any(const char* name, int m, int nnz, int replicas, float scale, const void* values,
+                       const int* row_indices, const int* row_offsets, void* out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (m < 0 || nnz < 0 || replicas < 0) return invalid("tsp_csr_softmax_f32: negative dimension");
-  if (replicas > 65535) return invalid("tsp_csr_softmax_f32: replicas=%d exceeds 65535", replicas);
+  if (m < 0 || nnz < 0 || replicas < 0) return invalid("%s: negative dimension", name);
+  if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
   if (m == 0 || nnz == 0 || replicas == 0) return TSP_OK;
-  if (!values || !row_offsets || !out) return invalid("tsp_csr_softmax_f32: null pointer argument");
-  SoftmaxArgs a;
+  if (!values || !row_offsets || !out) return invalid("%s: null pointer argument", name);
+  SoftmaxArgsT<T> a;
   a.m = m; a.nnz = nnz; a.scale = scale;
   a.row_indices = row_indices;
   a.row_offsets = row_offsets;
-  a.x = values; a.dy = nullptr; a.out = out;
+  a.x = static_cast<const T*>(values); a.dy = nullptr; a.out = static_cast<T*>(out);
   constexpr int WARPS = 8;
   dim3 grid(ceil_div(m, WARPS), replicas);
   switch (pick_softmax_reg(m, nnz)) {
-    case 4: csr_softmax_kernel<4, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
-    case 8: csr_softmax_kernel<8, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
-    case 16: csr_softmax_kernel<16, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
-    default: csr_softmax_kernel<32, WARPS><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 4: csr_softmax_kernel<4, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 8: csr_softmax_kernel<8, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 16: csr_softmax_kernel<16, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    default: csr_softmax_kernel<32, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
   }
-  TSP_CHECK_LAUNCH("tsp_csr_softmax_f32");
+  TSP_CHECK_LAUNCH(name);
   return TSP_OK;
+}
+
+extern "C" {
+
+int tsp_csr_softmax_f32(int m, int nnz, int replicas, float scale, const float* values,
+                        const int* row_indices, const int* row_offsets, float* out,
+                        void* stream_) {
+  return softmax_any<float>("tsp_csr_softmax_f32", m, nnz, replicas, scale, values, row_indices, row_offsets, out, stream_);
 }
 
 int tsp_sparse_attention_supported(int n, int d) {
@@ -588,9 +608,126 @@ int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int
   if (nnz == 0 || replicas == 0) return TSP_OK;
   if (!values || !perm || !values_t) return invalid("tsp_permute_values_f32: null pointer argument");
   dim3 grid(ceil_div(nnz, 256), replicas);
-  permute_values_kernel<<<grid, 256, 0, stream>>>(nnz, values, perm, values_t);
+  permute_values_kernel<float><<<grid, 256, 0, stream>>>(nnz, values, perm, values_t);
   TSP_CHECK_LAUNCH("tsp_permute_values_f32");
   return TSP_OK;
+}
+
+int tsp_permute_values_b16(int nnz, int replicas, const void* values, const int* perm, void* values_t,
+                           void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (nnz < 0 || replicas < 0) return invalid("tsp_permute_values_b16: negative dimension");
+  if (replicas > 65535) return invalid("tsp_permute_values_b16: replicas=%d exceeds 65535", replicas);
+  if (nnz == 0 || replicas == 0) return TSP_OK;
+  if (!values || !perm || !values_t) return invalid("tsp_permute_values_b16: null pointer argument");
+  dim3 grid(ceil_div(nnz, 256), replicas);
+  permute_values_kernel<unsigned short><<<grid, 256, 0, stream>>>(
+      nnz, static_cast<const unsigned short*>(values), perm, static_cast<unsigned short*>(values_t));
+  TSP_CHECK_LAUNCH("tsp_permute_values_b16");
+  return TSP_OK;
+}
+
+// ------------------------------------------------------------ 16-bit storage, fp32 arithmetic
+// (all gather-type kernels: no topology views, so no plan is involved)
+}  // extern "C"
+
+template <typename T>
+static int spmm_b16(const char* name, int m, int k, int n, int nnz, int replicas, int values_shared,
+                    const int* row_indices, const void* values, const int* value_perm_or_null,
+                    const int* row_offsets, const int* column_indices, const void* dense,
+                    const float* bias_or_null, int relu, void* out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("%s: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", name, m, k, n, nnz, replicas);
+  if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
+  if (m == 0 || n == 0 || replicas == 0) return TSP_OK;
+  if (!row_offsets || !out || (nnz > 0 && (!values || !column_indices || !dense)))
+    return invalid("%s: null pointer argument", name);
+  SpmmArgsT<T> a;
+  a.m = m; a.k = k; a.n = n; a.nnz = nnz;
+  a.values_stride = values_shared ? 0 : (long long)nnz;
+  a.row_indices = row_indices;
+  a.values = static_cast<const T*>(values);
+  a.row_offsets = row_offsets;
+  a.column_indices = column_indices;
+  a.dense = static_cast<const T*>(dense);
+  a.bias = bias_or_null;
+  a.relu = relu;
+  a.out = static_cast<T*>(out);
+  a.value_perm = value_perm_or_null;
+  if (((reinterpret_cast<uintptr_t>(dense) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(values)) & 1u) != 0)
+    return invalid("%s: operands must be 2-byte aligned", name);
+  if (!spmm_rowsplit_applicable(a)) return invalid("%s: dense operand too large for 32-bit row offsets", name);
+  launch_spmm_rowsplit<T>(a, replicas, stream);
+  TSP_CHECK_LAUNCH(name);
+  return TSP_OK;
+}
+
+template <typename T>
+static int sddmm_b16(const char* name, int m, int k, int n, int nnz, int replicas, const int* row_offsets,
+                     const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("%s: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", name, m, k, n, nnz, replicas);
+  if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
+  if (nnz == 0 || replicas == 0) return TSP_OK;
+  if (!row_offsets || !column_indices || !out || (k > 0 && (!lhs || !rhs)))
+    return invalid("%s: null pointer argument", name);
+  SddmmArgsT<T> a;
+  a.m = m; a.k = k; a.n = n; a.nnz = nnz;
+  a.row_offsets = row_offsets;
+  a.column_indices = column_indices;
+  a.lhs = static_cast<const T*>(lhs);
+  a.rhs = static_cast<const T*>(rhs);
+  a.out = static_cast<T*>(out);
+  if (g_sddmm_variant.load() != 1 && sddmm_rows_applicable(a)) {
+    launch_sddmm_rows<T>(a, replicas, stream);
+  } else if (k % 8 == 0 && aligned16(lhs) && aligned16(rhs)) {
+    if (k <= 64) launch_sddmm_gather<8, 8, T>(a, replicas, stream);
+    else if (k <= 128) launch_sddmm_gather<8, 16, T>(a, replicas, stream);
+    else launch_sddmm_gather<8, 32, T>(a, replicas, stream);
+  } else {
+    if (k <= 8) launch_sddmm_gather<1, 8, T>(a, replicas, stream);
+    else if (k <= 16) launch_sddmm_gather<1, 16, T>(a, replicas, stream);
+    else launch_sddmm_gather<1, 32, T>(a, replicas, stream);
+  }
+  TSP_CHECK_LAUNCH(name);
+  return TSP_OK;
+}
+
+extern "C" {
+
+int tsp_spmm_f16(int m, int k, int n, int nnz, int replicas, int values_shared, const int* row_indices,
+                 const void* values, const int* value_perm_or_null, const int* row_offsets,
+                 const int* column_indices, const void* dense, const float* bias_or_null, int relu,
+                 void* out, void* stream) {
+  return spmm_b16<__half>("tsp_spmm_f16", m, k, n, nnz, replicas, values_shared, row_indices, values, value_perm_or_null,
+                          row_offsets, column_indices, dense, bias_or_null, relu, out, stream);
+}
+int tsp_spmm_bf16(int m, int k, int n, int nnz, int replicas, int values_shared, const int* row_indices,
+                  const void* values, const int* value_perm_or_null, const int* row_offsets,
+                  const int* column_indices, const void* dense, const float* bias_or_null, int relu,
+                  void* out, void* stream) {
+  return spmm_b16<__nv_bfloat16>("tsp_spmm_bf16", m, k, n, nnz, replicas, values_shared, row_indices, values,
+                                 value_perm_or_null, row_offsets, column_indices, dense, bias_or_null, relu, out, stream);
+}
+int tsp_sddmm_f16(int m, int k, int n, int nnz, int replicas, const int* row_indices, const int* row_offsets,
+                  const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream) {
+  (void)row_indices;
+  return sddmm_b16<__half>("tsp_sddmm_f16", m, k, n, nnz, replicas, row_offsets, column_indices, lhs, rhs, out, stream);
+}
+int tsp_sddmm_bf16(int m, int k, int n, int nnz, int replicas, const int* row_indices, const int* row_offsets,
+                   const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream) {
+  (void)row_indices;
+  return sddmm_b16<__nv_bfloat16>("tsp_sddmm_bf16", m, k, n, nnz, replicas, row_offsets, column_indices, lhs, rhs, out, stream);
+}
+int tsp_csr_softmax_f16(int m, int nnz, int replicas, float scale, const void* values, const int* row_indices,
+                        const int* row_offsets, void* out, void* stream) {
+  return softmax_any<__half>("tsp_csr_softmax_f16", m, nnz, replicas, scale, values, row_indices, row_offsets, out, stream);
+}
+int tsp_csr_softmax_bf16(int m, int nnz, int replicas, float scale, const void* values, const int* row_indices,
+                         const int* row_offsets, void* out, void* stream) {
+  return softmax_any<__nv_bfloat16>("tsp_csr_softmax_bf16", m, nnz, replicas, scale, values, row_indices, row_offsets, out, stream);
 }
 
 }  // extern "C"
