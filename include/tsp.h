@@ -145,6 +145,13 @@ int tsp_csr_softmax_backward_f32(int m, int nnz, int replicas, float scale,
  * (d = 32, 64, 96, 128 and n * d < 2^29); operands must be 16-byte aligned.
  */
 int tsp_sparse_attention_supported(int n, int d);
+/* 16-bit storage (bf16 == 0: fp16, != 0: bfloat16): head dimension 64, 128, 192 or 256; scores,
+ * probabilities, the running maximum and all sums fp32; out rounded once; lse stays fp32. */
+int tsp_sparse_attention_supported_b16(int n, int d);
+int tsp_sparse_attention_b16(int bf16, int m, int n, int d, int nnz, int replicas, float scale,
+                             const int* row_indices, const int* row_offsets,
+                             const int* column_indices, const void* q, const void* k,
+                             const void* v, void* out, float* lse_or_null, void* stream);
 int tsp_sparse_attention_f32(int m, int n, int d, int nnz, int replicas, float scale,
                              const int* row_indices, const int* row_offsets,
                              const int* column_indices, const float* q, const float* k,
@@ -244,6 +251,13 @@ int tsp_plan_spmm_f32(tsp_plan* plan, int n, int replicas, int values_shared,
                       void* stream);
 int tsp_plan_sddmm_f32(tsp_plan* plan, int k, int replicas, int reduce, const int* row_indices,
                        const float* lhs, const float* rhs, float* out, void* stream);
+/* 16-bit storage on a plan: bf16 == 0 -> fp16 elements, != 0 -> bfloat16 (see tsp_spmm_f16). */
+int tsp_plan_spmm_b16(tsp_plan* plan, int bf16, int n, int replicas, int values_shared,
+                      const int* row_indices, const void* values, const int* value_perm_or_null,
+                      const void* dense, const float* bias_or_null, int relu, void* out,
+                      void* stream);
+int tsp_plan_sddmm_b16(tsp_plan* plan, int bf16, int k, int replicas, const int* row_indices,
+                       const void* lhs, const void* rhs, void* out, void* stream);
 
 /*
  * Knobs for A/B benchmarking only (not part of the reference surface):

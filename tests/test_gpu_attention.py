@@ -95,3 +95,27 @@ def test_fused_attention_unsupported_head_dim_uses_chain():
     ref, _ = _oracle_attention(a, q, k, v, 0.2)
     np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=1e-5, atol=1e-5)
     assert lse.numel() == 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m,n,d,dens,reps", [(128, 128, 64, 0.1, 3), (200, 333, 128, 0.3, 2), (64, 512, 256, 0.5, 1),
+                                             (77, 150, 192, 0.1, 2)])
+def test_fused_attention_16bit_storage(dtype, m, n, d, dens, reps):
+    """q / k / v / out in fp16 or bf16, scores / probabilities / sums fp32: against the fp64 chain on the
+    same (exactly representable) inputs, within one rounding of the result + the fp32 chain's 1e-5."""
+    import torch_sputnik_b200 as tsp
+    dev = torch.device("cuda:0")
+    a = random_csr(m, n, dens, seed=m + d, values="pm1")
+    a_rows = np.diff(a.row_offsets)
+    ri, ro, ci = _dev(a, dev)
+    q, k, v = (torch.from_numpy(dense_operand((reps, rows, d), sd, "pm1")).to(dev).to(dtype)
+               for rows, sd in ((m, 1), (n, 2), (n, 3)))
+    scale = 1.0 / np.sqrt(d)
+    out, lse = tsp.sparse_attention(m, n, ri, ro, ci, q, k, v, scale)
+    assert out.dtype == dtype and lse.dtype == torch.float32 and tuple(lse.shape) == (reps, m)
+    eps = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+    for r in range(reps):
+        ref, _ = _oracle_attention(a, *(x[r].float().cpu().numpy() for x in (q, k, v)), scale)
+        got = out[r].float().cpu().numpy()
+        assert np.all(np.abs(got - ref) <= eps * np.abs(ref) + 2e-5), float(np.abs(got - ref).max())
+    assert bool(torch.isinf(lse[:, torch.from_numpy(a_rows == 0).to(dev)]).all())

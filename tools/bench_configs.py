@@ -224,12 +224,17 @@ def c4(dev, flush, replicas):
     total = ms_sddmm + ms_soft + ms_spmm
     emit("C4", "attention fwd (3 ops)", total, r * (16 * nnz + 16 * s * d) + 2 * topo + 4 * (2 * s + 1),
          4.0 * nnz * d * r, {"replicas_per_gpu": r, "replicas_total": replicas})
-    # fp32 SpMM through the row-split kernel (variant 5) for an A/B against the gather kernel
-    ops.set_variant("spmm", 5)
-    ms_rs = timeit(lambda: ops.spmm(s, s, probs, ri, ro, ci, vv))
+    # A/B: the L1-gather kernels the band kernels replace at this shape
+    ops.set_variant("spmm", 1)
+    ms_g = timeit(lambda: ops.spmm(s, s, probs, ri, ro, ci, vv))
     ops.set_variant("spmm", 0)
-    emit("C4", "spmm (row-split kernel, fp32)", ms_rs, r * (4 * nnz + 8 * s * d) + topo, 2.0 * nnz * d * r,
-         {"replicas_per_gpu": r, "gather_ms": round(ms_spmm, 4)})
+    ops.set_variant("sddmm", 5)
+    ms_r = timeit(lambda: ops.sddmm(s, s, ri, ro, ci, q, kk))
+    ops.set_variant("sddmm", 0)
+    emit("C4", "spmm (gather kernel, fp32)", ms_g, r * (4 * nnz + 8 * s * d) + topo, 2.0 * nnz * d * r,
+         {"replicas_per_gpu": r, "band_ms": round(ms_spmm, 4)})
+    emit("C4", "sddmm (rows kernel, fp32)", ms_r, r * (4 * nnz + 8 * s * d) + topo, 2.0 * nnz * d * r,
+         {"replicas_per_gpu": r, "band_ms": round(ms_sddmm, 4)})
     # 16-bit storage, fp32 arithmetic: the same three ops (algorithmic bytes halve, topology stays int32)
     for name, dt in (("f16", torch.float16), ("bf16", torch.bfloat16)):
         qh, kh, vh = q.to(dt), kk.to(dt), vv.to(dt)

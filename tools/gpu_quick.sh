@@ -1,4 +1,6 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-CUDA_LAUNCH_BLOCKING=1 python tests/golden/make_golden_gpu.py --half gpurun_out/ref_b200_f16.npz 2>&1 | tail -25
+timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
+tail -8 gpurun_out/pytest_gpu.log
+timeout 600 python tools/ab_band.py 2>&1 | tee gpurun_out/ab_band.jsonl

@@ -17,7 +17,7 @@ R = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 if os.environ.get("TSP_VARIANT") and op != "attn":
     ops.set_variant(op, int(os.environ["TSP_VARIANT"]))
-for knob in ("spmm_warps", "sddmm_warps", "attn_warps"):
+for knob in ("spmm_warps", "sddmm_warps", "attn_warps", "band_warps"):
     if os.environ.get("TSP_" + knob.upper()):
         ops.set_variant(knob, int(os.environ["TSP_" + knob.upper()]))
 dev = torch.device("cuda:0")

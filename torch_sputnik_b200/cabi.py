@@ -17,7 +17,8 @@ SYMBOLS = (
     "tsp_plan_create", "tsp_plan_destroy", "tsp_plan_sorted", "tsp_plan_transpose", "tsp_plan_spmm_f32",
     "tsp_plan_sddmm_f32",
     "tsp_spmm_f16", "tsp_spmm_bf16", "tsp_sddmm_f16", "tsp_sddmm_bf16", "tsp_csr_softmax_f16", "tsp_csr_softmax_bf16",
-    "tsp_permute_values_b16",
+    "tsp_permute_values_b16", "tsp_plan_spmm_b16", "tsp_plan_sddmm_b16",
+    "tsp_sparse_attention_supported_b16", "tsp_sparse_attention_b16",
 )
 
 _lib = None
@@ -44,6 +45,8 @@ def load() -> ctypes.CDLL:
         lib.tsp_permute_values_f32.argtypes = [i, i, vp, vp, vp, vp]
         lib.tsp_sparse_attention_supported.argtypes = [i, i]
         lib.tsp_sparse_attention_f32.argtypes = [i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        lib.tsp_sparse_attention_supported_b16.argtypes = [i, i]
+        lib.tsp_sparse_attention_b16.argtypes = [i, i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_set_variant.argtypes = [ctypes.c_char_p, i]
         lib.tsp_launch_count.restype = ctypes.c_ulonglong
         for name in ("tsp_spmm_f16", "tsp_spmm_bf16"):
@@ -61,6 +64,8 @@ def load() -> ctypes.CDLL:
         lib.tsp_plan_transpose.argtypes = [vp, vp, pp, pp, pp, pp]
         lib.tsp_plan_spmm_f32.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp, i, vp, vp]
         lib.tsp_plan_sddmm_f32.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp]
+        lib.tsp_plan_spmm_b16.argtypes = [vp, i, i, i, i, vp, vp, vp, vp, vp, i, vp, vp]
+        lib.tsp_plan_sddmm_b16.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp]
         _lib = lib
     return _lib
 

@@ -5,7 +5,8 @@
 // probabilities: 16 of the 18.5 bytes per nonzero that the three-kernel chain moves through HBM)
 // never exist.
 //
-// Shape of the work (head_dim d = 32, 64, 96 or 128): the same as sddmm_rows.cuh, twice.
+// Shape of the work (head_dim d = 32, 64, 96 or 128 in fp32; 64 .. 256 in fp16 / bf16 storage):
+// the same as sddmm_rows.cuh, twice.
 //  * one warp owns one mask row; lane `sub` of each quarter-warp keeps the 16-byte chunks
 //    sub, sub+8, .. of q[row, :] (pre-multiplied by scale * log2 e) and of the output row;
 //  * nonzeros are taken 32 at a time.  Score phase: in step g quarter `qq` dots its q chunks with
@@ -26,21 +27,27 @@
 
 namespace tsp {
 
-struct AttnArgs {
+// T: storage type of q / k / v / out (float, __half, __nv_bfloat16); scores, probabilities and sums fp32.
+template <typename T>
+struct AttnArgsT {
   int m, n, d, nnz;
   const int* row_offsets;
   const int* column_indices;
-  const float* q;   // [replicas, m, d]
-  const float* k;   // [replicas, n, d]
-  const float* v;   // [replicas, n, d]
-  float* out;       // [replicas, m, d]
-  float* lse;       // optional [replicas, m]: log(sum exp(scale * score)) per row (natural log)
+  const T* q;    // [replicas, m, d]
+  const T* k;    // [replicas, n, d]
+  const T* v;    // [replicas, n, d]
+  T* out;        // [replicas, m, d]
+  float* lse;    // optional [replicas, m]: log(sum exp(scale * score)) per row (natural log)
   float scale;
 };
+using AttnArgs = AttnArgsT<float>;
 
-template <int KC, int WARPS>   // d = 32 * KC
-__global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnArgs a) {
-  constexpr int D = 32 * KC;
+// d = 8 * E * KC with E elements per 16-byte chunk (4 fp32 / 8 16-bit): a quarter-warp covers 128
+// bytes of a k / v row per step, so 16-bit storage halves the L1 wavefronts per nonzero.
+template <int KC, int WARPS, typename T = float>
+__global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnArgsT<T> a) {
+  constexpr int E = Elem<T>::kPer16;
+  constexpr int D = 8 * E * KC;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * WARPS + warp;
   if (row >= a.m) return;
@@ -48,35 +55,41 @@ __global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnAr
   const int qq = lane >> 3, sub = lane & 7;
 
   const int beg = __ldg(a.row_offsets + row), end = __ldg(a.row_offsets + row + 1);
-  float4* const orow = reinterpret_cast<float4*>(a.out + ((size_t)rep * a.m + row) * D) + sub;
+  T* const orow = a.out + ((size_t)rep * a.m + row) * D + sub * E;
   if (beg >= end) {
     if (qq == 0) {
+      float z[E];
 #pragma unroll
-      for (int cc = 0; cc < KC; ++cc) orow[cc * 8] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int e = 0; e < E; ++e) z[e] = 0.f;
+#pragma unroll
+      for (int cc = 0; cc < KC; ++cc) store_elems<T, E>(orow + cc * 8 * E, z);
     }
     if (a.lse != nullptr && lane == 0) a.lse[(size_t)rep * a.m + row] = -INFINITY;
     return;
   }
   const int* __restrict__ cols = a.column_indices;
-  const float4* const kbase = reinterpret_cast<const float4*>(a.k + (size_t)rep * a.n * D) + sub;
-  const float4* const vbase = reinterpret_cast<const float4*>(a.v + (size_t)rep * a.n * D) + sub;
-  const float4* const qrow = reinterpret_cast<const float4*>(a.q + ((size_t)rep * a.m + row) * D) + sub;
+  const T* const kbase = a.k + (size_t)rep * a.n * D + sub * E;
+  const T* const vbase = a.v + (size_t)rep * a.n * D + sub * E;
+  const T* const qrow = a.q + ((size_t)rep * a.m + row) * D + sub * E;
   const float qs = a.scale * 1.4426950408889634f;
-  float4 qv[KC], acc[KC];
+  float qv[KC][E], acc[KC][E];
 #pragma unroll
   for (int cc = 0; cc < KC; ++cc) {
-    const float4 x = __ldg(qrow + cc * 8);
-    qv[cc] = make_float4(x.x * qs, x.y * qs, x.z * qs, x.w * qs);
-    acc[cc] = make_float4(0.f, 0.f, 0.f, 0.f);
+    load_elems<T, E>(qv[cc], qrow + cc * 8 * E);
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      qv[cc][e] *= qs;
+      acc[cc][e] = 0.f;
+    }
   }
   float run_max = -INFINITY;   // warp-uniform, in log2 units
   float denom = 0.f;           // this lane's share of the denominator, relative to run_max
 
   for (int p = beg; p < end; p += 32) {
     const int cnt = min(32, end - p);
-    // rows of k / v in float4 units; lanes past the end of the row repeat its last nonzero (a valid
+    // rows of k / v in 16-byte units; lanes past the end of the row repeat its last nonzero (a valid
     // address whose probability is forced to zero below)
-    const unsigned myoff = (unsigned)__ldg(cols + p + min(lane, cnt - 1)) * (unsigned)(D / 4);
+    const unsigned myoff = (unsigned)__ldg(cols + p + min(lane, cnt - 1)) * (unsigned)(8 * KC);
     float s[8];
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
@@ -86,11 +99,10 @@ __global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnAr
         float t = 0.f;
 #pragma unroll
         for (int cc = 0; cc < KC; ++cc) {
-          const float4 x = __ldg(kbase + off + cc * 8);
-          t = fmaf(qv[cc].x, x.x, t);
-          t = fmaf(qv[cc].y, x.y, t);
-          t = fmaf(qv[cc].z, x.z, t);
-          t = fmaf(qv[cc].w, x.w, t);
+          float x[E];
+          load_elems<T, E>(x, kbase + ((size_t)off + cc * 8) * E);
+#pragma unroll
+          for (int e = 0; e < E; ++e) t = fmaf(qv[cc][e], x[e], t);
         }
         s[g] = t;
       }
@@ -103,12 +115,9 @@ __global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnAr
     denom = fmaf(denom, corr, prob);
     run_max = new_max;
 #pragma unroll
-    for (int cc = 0; cc < KC; ++cc) {
-      acc[cc].x *= corr;
-      acc[cc].y *= corr;
-      acc[cc].z *= corr;
-      acc[cc].w *= corr;
-    }
+    for (int cc = 0; cc < KC; ++cc)
+#pragma unroll
+      for (int e = 0; e < E; ++e) acc[cc][e] *= corr;
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
       if (4 * g < cnt) {
@@ -116,11 +125,10 @@ __global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnAr
         const float w = __shfl_sync(kFullMask, prob, 8 * qq + g);
 #pragma unroll
         for (int cc = 0; cc < KC; ++cc) {
-          const float4 x = __ldg(vbase + off + cc * 8);
-          acc[cc].x = fmaf(w, x.x, acc[cc].x);
-          acc[cc].y = fmaf(w, x.y, acc[cc].y);
-          acc[cc].z = fmaf(w, x.z, acc[cc].z);
-          acc[cc].w = fmaf(w, x.w, acc[cc].w);
+          float x[E];
+          load_elems<T, E>(x, vbase + ((size_t)off + cc * 8) * E);
+#pragma unroll
+          for (int e = 0; e < E; ++e) acc[cc][e] = fmaf(w, x[e], acc[cc][e]);
         }
       }
     }
@@ -130,48 +138,51 @@ __global__ void __launch_bounds__(WARPS * 32) attention_rows_kernel(const AttnAr
   const float inv = 1.0f / total;
 #pragma unroll
   for (int cc = 0; cc < KC; ++cc) {
-    float4 t = acc[cc];
+    float t[E];
 #pragma unroll
-    for (int o = 8; o <= 16; o <<= 1) {
-      t.x += __shfl_xor_sync(kFullMask, t.x, o);
-      t.y += __shfl_xor_sync(kFullMask, t.y, o);
-      t.z += __shfl_xor_sync(kFullMask, t.z, o);
-      t.w += __shfl_xor_sync(kFullMask, t.w, o);
+    for (int e = 0; e < E; ++e) {
+      float x = acc[cc][e];
+      x += __shfl_xor_sync(kFullMask, x, 8);
+      x += __shfl_xor_sync(kFullMask, x, 16);
+      t[e] = x * inv;
     }
-    if (qq == (cc & 3)) orow[cc * 8] = make_float4(t.x * inv, t.y * inv, t.z * inv, t.w * inv);
+    if (qq == (cc & 3)) store_elems<T, E>(orow + cc * 8 * E, t);
   }
   if (a.lse != nullptr && lane == 0)
     a.lse[(size_t)rep * a.m + row] = (run_max + log2f(total)) * 0.6931471805599453f;
 }
 
-inline bool attention_rows_applicable(const AttnArgs& a) {
-  if (a.d % 32 != 0 || a.d > 128 || a.d < 32) return false;
+template <typename T>
+inline bool attention_rows_applicable(const AttnArgsT<T>& a) {
+  constexpr int chunk = 8 * Elem<T>::kPer16;
+  if (a.d % chunk != 0 || a.d > 4 * chunk || a.d < chunk) return false;
   if (!aligned16(a.q) || !aligned16(a.k) || !aligned16(a.v) || !aligned16(a.out)) return false;
-  return (unsigned long long)a.n * (unsigned long long)a.d * 4ull < (1ull << 31);
+  return (unsigned long long)a.n * (unsigned long long)a.d * sizeof(T) < (1ull << 31);
 }
 
 extern std::atomic<int> g_attn_warps;   // benchmark knob "attn_warps": rows per CTA (0 = default)
 
-template <int KC, int WARPS>
-inline void launch_attention_rows_w(const AttnArgs& a, int replicas, cudaStream_t stream) {
-  attention_rows_kernel<KC, WARPS><<<dim3(ceil_div(a.m, WARPS), replicas), WARPS * 32, 0, stream>>>(a);
+template <int KC, int WARPS, typename T>
+inline void launch_attention_rows_w(const AttnArgsT<T>& a, int replicas, cudaStream_t stream) {
+  attention_rows_kernel<KC, WARPS, T><<<dim3(ceil_div(a.m, WARPS), replicas), WARPS * 32, 0, stream>>>(a);
 }
 
-template <int KC>
-inline void launch_attention_rows_kc(const AttnArgs& a, int replicas, cudaStream_t stream) {
+template <int KC, typename T>
+inline void launch_attention_rows_kc(const AttnArgsT<T>& a, int replicas, cudaStream_t stream) {
   const int w = g_attn_warps.load();
-  if (w == 4) launch_attention_rows_w<KC, 4>(a, replicas, stream);
-  else if (w == 8) launch_attention_rows_w<KC, 8>(a, replicas, stream);
-  else if (w == 16) launch_attention_rows_w<KC, 16>(a, replicas, stream);
-  else launch_attention_rows_w<KC, 32>(a, replicas, stream);
+  if (w == 4) launch_attention_rows_w<KC, 4, T>(a, replicas, stream);
+  else if (w == 8) launch_attention_rows_w<KC, 8, T>(a, replicas, stream);
+  else if (w == 16) launch_attention_rows_w<KC, 16, T>(a, replicas, stream);
+  else launch_attention_rows_w<KC, 32, T>(a, replicas, stream);
 }
 
-inline void launch_attention_rows(const AttnArgs& a, int replicas, cudaStream_t stream) {
-  switch (a.d / 32) {
-    case 1: launch_attention_rows_kc<1>(a, replicas, stream); break;
-    case 2: launch_attention_rows_kc<2>(a, replicas, stream); break;
-    case 3: launch_attention_rows_kc<3>(a, replicas, stream); break;
-    default: launch_attention_rows_kc<4>(a, replicas, stream); break;
+template <typename T>
+inline void launch_attention_rows(const AttnArgsT<T>& a, int replicas, cudaStream_t stream) {
+  switch (a.d / (8 * Elem<T>::kPer16)) {
+    case 1: launch_attention_rows_kc<1, T>(a, replicas, stream); break;
+    case 2: launch_attention_rows_kc<2, T>(a, replicas, stream); break;
+    case 3: launch_attention_rows_kc<3, T>(a, replicas, stream); break;
+    default: launch_attention_rows_kc<4, T>(a, replicas, stream); break;
   }
 }
 

@@ -36,6 +36,7 @@ template <int KC, int WARPS, typename T = float>
 __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT<T> a) {
   constexpr int E = Elem<T>::kPer16;
   constexpr int K = 8 * E * KC;
+  if (fallback_not_needed(a.guard_flag)) return;   // queued behind a band launch whose guard held
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * WARPS + warp;
   if (row >= a.m) return;

@@ -26,10 +26,14 @@
 
 namespace tsp {
 
+// (Measured and dropped: sending a 16-bit value and its column between lanes as ONE packed word --
+// one shuffle per step instead of two -- is slower, 2.51 vs 2.31 ms at the C4 shape: the unpacking
+// costs more issue slots than the shuffle it saves.  profiles/r02_band_ab.txt)
 template <typename T, int EPL, int LPN, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArgsT<T> a) {
   constexpr int G = 32 / LPN;
   constexpr int UNR = LPN >= 4 ? 4 : LPN;   // gathered loads in flight per lane
+  if (fallback_not_needed(a.guard_flag)) return;   // queued behind a band launch whose guard held
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int item = blockIdx.x * WARPS + warp;
   if (item >= a.m) return;

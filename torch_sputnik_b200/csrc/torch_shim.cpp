@@ -298,6 +298,13 @@ torch::Tensor spmm_impl(int64_t m, int64_t k, const torch::Tensor& values_in,
                                               : torch::empty({m, n}, options);
   if (dtype != torch::kFloat32) {
     // 16-bit storage, fp32 arithmetic, result in the storage type (cuda_spmm.h:75-127)
+    if (auto e = get_plan(m, k, row_offsets, column_indices)) {
+      check_rc(tsp_plan_spmm_b16(e->plan, dtype == torch::kBFloat16 ? 1 : 0, (int)n, (int)replicas, shared ? 1 : 0,
+                                 row_indices.data_ptr<int>(), values.data_ptr(), perm_ptr, dense.data_ptr(), bias_ptr,
+                                 relu ? 1 : 0, out.data_ptr(), current_stream()),
+               op);
+      return out;
+    }
     auto fn = dtype == torch::kFloat16 ? tsp_spmm_f16 : tsp_spmm_bf16;
     check_rc(fn((int)m, (int)k, (int)n, (int)nnz, (int)replicas, shared ? 1 : 0, row_indices.data_ptr<int>(),
                 values.data_ptr(), perm_ptr, row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
@@ -377,6 +384,13 @@ static torch::Tensor sddmm_impl(int m, int n, const torch::Tensor& row_indices_i
                                                 : torch::empty({replicas, nnz}, options);
   const char* op = reduce ? "sddmm_reduce" : "sddmm";
   if (dtype != torch::kFloat32) {
+    if (auto e = get_plan(m, n, row_offsets, column_indices)) {
+      check_rc(tsp_plan_sddmm_b16(e->plan, dtype == torch::kBFloat16 ? 1 : 0, (int)k, (int)replicas,
+                                  row_indices.data_ptr<int>(), lhs.data_ptr(), rhs.data_ptr(), out.data_ptr(),
+                                  current_stream()),
+               op);
+      return out;
+    }
     auto fn16 = dtype == torch::kFloat16 ? tsp_sddmm_f16 : tsp_sddmm_bf16;
     check_rc(fn16(m, (int)k, n, (int)nnz, (int)replicas, row_indices.data_ptr<int>(), row_offsets.data_ptr<int>(),
                   column_indices.data_ptr<int>(), lhs.data_ptr(), rhs.data_ptr(), out.data_ptr(), current_stream()),
@@ -615,11 +629,12 @@ torch::Tensor spmm_perm(int m, int k, torch::Tensor values, torch::Tensor perm, 
 // k and v [R, n, d] (or 2-D for R = 1) -> [out [R, m, d], lse [R, m]].  Head dimensions the fused
 // kernel does not take go through the three-op chain (lse is then left empty).
 std::vector<torch::Tensor> sparse_attention(int m, int n, torch::Tensor row_indices_in, torch::Tensor row_offsets,
-                                            torch::Tensor column_indices, torch::Tensor q, torch::Tensor k,
-                                            torch::Tensor v, double scale) {
-  TSP_CHECK_CUDA_F32(q, "q");
-  TSP_CHECK_CUDA_F32(k, "k");
-  TSP_CHECK_CUDA_F32(v, "v");
+                                            torch::Tensor column_indices, torch::Tensor q_in, torch::Tensor k_in,
+                                            torch::Tensor v_in, double scale) {
+  torch::Tensor q = value_operand(q_in, "q"), k = value_operand(k_in, "k"), v = value_operand(v_in, "v");
+  TORCH_CHECK(q.scalar_type() == k.scalar_type() && q.scalar_type() == v.scalar_type(),
+              "torch_sputnik.sparse_attention: q, k, v must have the same dtype");
+  const auto dtype = q.scalar_type();
   TORCH_CHECK(q.dim() == k.dim() && q.dim() == v.dim() && (q.dim() == 2 || q.dim() == 3),
               "torch_sputnik.sparse_attention: q, k, v must all be 2-D or all 3-D");
   c10::cuda::CUDAGuard guard(q.device());
@@ -633,20 +648,30 @@ std::vector<torch::Tensor> sparse_attention(int m, int n, torch::Tensor row_indi
   const int64_t nnz = column_indices.size(0);
   const bool aligned = ((reinterpret_cast<uintptr_t>(q.data_ptr()) | reinterpret_cast<uintptr_t>(k.data_ptr()) |
                          reinterpret_cast<uintptr_t>(v.data_ptr())) & 15) == 0;
-  if (!aligned || !tsp_sparse_attention_supported(n, (int)d)) {
+  const bool fused = aligned && (dtype == torch::kFloat32 ? tsp_sparse_attention_supported(n, (int)d)
+                                                          : tsp_sparse_attention_supported_b16(n, (int)d));
+  if (!fused) {
     torch::Tensor scores = sddmm_impl(m, n, row_indices, row_offsets, column_indices, q, k, false);
     torch::Tensor probs = softmax_impl(scores, row_indices, row_offsets, column_indices, scale);
     torch::Tensor out = spmm_impl(m, n, probs, row_indices, row_offsets, column_indices, v, c10::nullopt, false,
                                   false, "sparse_attention");
-    return {out.reshape(q.sizes()), torch::empty({0}, q.options())};
+    return {out.reshape(q.sizes()), torch::empty({0}, q.options().dtype(torch::kFloat32))};
   }
   torch::Tensor out = torch::empty_like(q);
-  torch::Tensor lse = torch::empty(off ? std::vector<int64_t>{replicas, m} : std::vector<int64_t>{m}, q.options());
-  check_rc(tsp_sparse_attention_f32(m, n, (int)d, (int)nnz, (int)replicas, (float)scale, row_indices.data_ptr<int>(),
-                                    row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
-                                    q.data_ptr<float>(), k.data_ptr<float>(), v.data_ptr<float>(),
-                                    out.data_ptr<float>(), lse.data_ptr<float>(), current_stream()),
-           "sparse_attention");
+  torch::Tensor lse = torch::empty(off ? std::vector<int64_t>{replicas, m} : std::vector<int64_t>{m},
+                                   q.options().dtype(torch::kFloat32));
+  if (dtype == torch::kFloat32)
+    check_rc(tsp_sparse_attention_f32(m, n, (int)d, (int)nnz, (int)replicas, (float)scale, row_indices.data_ptr<int>(),
+                                      row_offsets.data_ptr<int>(), column_indices.data_ptr<int>(),
+                                      q.data_ptr<float>(), k.data_ptr<float>(), v.data_ptr<float>(),
+                                      out.data_ptr<float>(), lse.data_ptr<float>(), current_stream()),
+             "sparse_attention");
+  else
+    check_rc(tsp_sparse_attention_b16(dtype == torch::kBFloat16 ? 1 : 0, m, n, (int)d, (int)nnz, (int)replicas,
+                                      (float)scale, row_indices.data_ptr<int>(), row_offsets.data_ptr<int>(),
+                                      column_indices.data_ptr<int>(), q.data_ptr(), k.data_ptr(), v.data_ptr(),
+                                      out.data_ptr(), lse.data_ptr<float>(), current_stream()),
+             "sparse_attention");
   return {out, lse};
 }
 

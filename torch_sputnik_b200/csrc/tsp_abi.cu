@@ -17,6 +17,7 @@
 #include "kernels/sddmm_sampled.cuh"
 #include "kernels/sddmm_rows.cuh"
 #include "kernels/attention_rows.cuh"
+#include "kernels/band.cuh"
 #include "kernels/plan.cuh"
 
 namespace tsp {
@@ -27,6 +28,7 @@ static std::atomic<int> g_spmm_variant{0};
 std::atomic<int> g_spmm_warps{0};
 std::atomic<int> g_sddmm_warps{0};
 std::atomic<int> g_attn_warps{0};
+std::atomic<int> g_band_warps{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_spmm_rowsplit_max_n{0};   // fp32 operands up to this many columns take spmm_rowsplit
 static std::atomic<int> g_sddmm_bn{0};
@@ -77,6 +79,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm_rowsplit_max_n") == 0) return g_spmm_rowsplit_max_n.exchange(variant);
   if (op && strcmp(op, "spmm_warps") == 0) return g_spmm_warps.exchange(variant);
   if (op && strcmp(op, "sddmm_warps") == 0) return g_sddmm_warps.exchange(variant);
+  if (op && strcmp(op, "band_warps") == 0) return g_band_warps.exchange(variant);
   if (op && strcmp(op, "attn_warps") == 0) return g_attn_warps.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
@@ -169,6 +172,46 @@ int tsp_plan_transpose(tsp_plan* plan, void* stream_, tsp_plan** transposed_out,
   return TSP_OK;
 }
 
+}  // extern "C"
+
+// ---------------------------------------------------------------- band kernels (band.cuh)
+// Convention of the staged attempts:  0: the kernel wrote the result for certain (columns known
+// sorted);  1: launched under the plan's device guard -- the caller queues the guarded fallback
+// (guard_flag is set in the arguments);  -1: not launched;  > 1: error code + 1.
+template <typename T>
+static int try_sddmm_band(tsp_plan* plan, SddmmArgsT<T>& a, int replicas, cudaStream_t stream) {
+  StagedGuard guard;
+  int rc = 0;
+  const int gs = plan_guard(plan, stream, &guard, &rc);
+  if (rc != 0) return rc + 1;
+  if (gs == kGuardUnsorted) return -1;
+  if ((rc = plan_flush_check(plan, stream)) != 0) return rc + 1;
+  if ((rc = launch_sddmm_band<T>(a, replicas, stream, guard)) != 0) return rc + 1;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return cuda_fail(e, "tsp_sddmm (band)") + 1;
+  if (gs == kGuardSorted) return 0;
+  a.guard_flag = guard.flag;
+  return 1;
+}
+
+template <typename T>
+static int try_spmm_band(tsp_plan* plan, SpmmArgsT<T>& a, int replicas, cudaStream_t stream) {
+  StagedGuard guard;
+  int rc = 0;
+  const int gs = plan_guard(plan, stream, &guard, &rc);
+  if (rc != 0) return rc + 1;
+  if (gs == kGuardUnsorted) return -1;
+  if ((rc = plan_flush_check(plan, stream)) != 0) return rc + 1;
+  if ((rc = launch_spmm_band<T>(a, replicas, stream, guard)) != 0) return rc + 1;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) return cuda_fail(e, "tsp_spmm (band)") + 1;
+  if (gs == kGuardSorted) return 0;
+  a.guard_flag = guard.flag;
+  return 1;
+}
+
+extern "C" {
+
 // ------------------------------------------------------------------------------------ SpMM
 static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, const int* row_indices,
                      const float* values, const int* value_perm_or_null, const float* dense,
@@ -195,6 +238,14 @@ static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, con
   a.value_perm = value_perm_or_null;
 
   const int variant = g_spmm_variant.load();
+  // variant 6: the band kernel wherever its shape allows; 0: where it is expected to win; 7: never.
+  if ((variant == 6 && band_kc<float>(n) != 0 && aligned16(dense) && aligned16(out)) ||
+      (variant == 0 && spmm_band_applicable(a, replicas))) {
+    const int st = try_spmm_band<float>(plan, a, replicas, stream);
+    if (st > 1) return st - 1;
+    if (st == 0) return TSP_OK;
+    // st == 1: the gather launch below is the guarded fallback; st == -1: it is the kernel
+  }
   const bool vec4_ok = (n % 4 == 0) && aligned16(dense) && aligned16(out);
   const bool vec2_ok = (n % 2 == 0) && ((reinterpret_cast<uintptr_t>(dense) & 7u) == 0) &&
                        ((reinterpret_cast<uintptr_t>(out) & 7u) == 0);
@@ -204,8 +255,8 @@ static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, con
   const double density = (double)nnz / ((double)m * (double)k);
   // Below ~22 % density (measured crossover on B200, profiles/) rows of a group share almost no columns, merging cannot raise the FMA
   // per shared-memory wavefront ratio, and the L1/L2 gather kernel has less fixed cost per slab.
-  const bool staged_ok = variant != 1 && spmm_staged_applicable(a, replicas) &&
-                         (variant != 0 || density >= 0.22);
+  const bool staged_ok = variant != 1 && a.guard_flag == nullptr && spmm_staged_applicable(a, replicas) &&
+                         (variant != 0 || density >= 0.22) && variant < 5;
   if (staged_ok) {
     StagedGuard guard;
     int rc = 0;
@@ -376,13 +427,20 @@ static int sddmm_core(tsp_plan* plan, int k, int replicas, const int* row_indice
   // 5 = rows (k <= 128).
   const bool want_tiled = variant == 2 || variant == 4 || (variant == 0 && density >= 0.22);   // 4 = tiled v1
   const bool want_sampled = variant == 3 || (variant == 0 && density >= 0.015 && density < 0.22);
+  // 6 = band (short inner dimension, operand blocks staged in shared memory); 0: where it should win
+  if ((variant == 6 && band_kc<float>(k) != 0 && aligned16(lhs) && aligned16(rhs)) ||
+      (variant == 0 && sddmm_band_applicable(a, replicas))) {
+    const int st = try_sddmm_band<float>(plan, a, replicas, stream);
+    if (st > 1) return st - 1;
+    if (st == 0) return TSP_OK;
+  }
   // 5 = rows (short inner dimension, k <= 128): no sortedness requirement, no fallback needed.
-  if ((variant == 5 || (variant == 0 && (k < 128 || density < 0.22))) && sddmm_rows_applicable(a)) {
+  if ((variant == 5 || variant == 6 || (variant == 0 && (k < 128 || density < 0.22))) && sddmm_rows_applicable(a)) {
     launch_sddmm_rows(a, replicas, stream);
     TSP_CHECK_LAUNCH("tsp_sddmm_f32 (rows)");
     return TSP_OK;
   }
-  const int st = sddmm_staged(plan, a, replicas, stream, want_tiled, variant == 4, want_sampled);
+  const int st = a.guard_flag != nullptr ? -1 : sddmm_staged(plan, a, replicas, stream, want_tiled, variant == 4, want_sampled);
   if (st > 1) return st - 1;
   if (st == 0) return TSP_OK;
   launch_sddmm_gather_any(a, replicas, stream);   // st == 1: guarded fallback; st == -1: the kernel
@@ -475,29 +533,56 @@ int tsp_sparse_attention_supported(int n, int d) {
          (unsigned long long)n * (unsigned long long)d * 4ull < (1ull << 31);
 }
 
+int tsp_sparse_attention_supported_b16(int n, int d) {
+  return d >= 64 && d <= 256 && d % 64 == 0 &&
+         (unsigned long long)n * (unsigned long long)d * 2ull < (1ull << 31);
+}
+
+}  // extern "C"
+
+template <typename T>
+static int sparse_attention_any(const char* name, int m, int n, int d, int nnz, int replicas, float scale,
+                                const int* row_offsets, const int* column_indices, const void* q,
+                                const void* k, const void* v, void* out, float* lse_or_null, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (m < 0 || n < 0 || d < 0 || nnz < 0 || replicas < 0) return invalid("%s: negative dimension", name);
+  if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
+  if (m == 0 || replicas == 0) return TSP_OK;
+  if (!(sizeof(T) == 4 ? tsp_sparse_attention_supported(n, d) : tsp_sparse_attention_supported_b16(n, d)))
+    return invalid("%s: head dimension %d (n=%d) not supported; use the three-op chain", name, d, n);
+  if (!row_offsets || !q || !k || !v || !out || (nnz > 0 && !column_indices))
+    return invalid("%s: null pointer argument", name);
+  AttnArgsT<T> a;
+  a.m = m; a.n = n; a.d = d; a.nnz = nnz;
+  a.row_offsets = row_offsets; a.column_indices = column_indices;
+  a.q = static_cast<const T*>(q); a.k = static_cast<const T*>(k); a.v = static_cast<const T*>(v);
+  a.out = static_cast<T*>(out); a.lse = lse_or_null; a.scale = scale;
+  if (!attention_rows_applicable(a)) return invalid("%s: q, k, v and out must be 16-byte aligned", name);
+  launch_attention_rows<T>(a, replicas, stream);
+  TSP_CHECK_LAUNCH(name);
+  return TSP_OK;
+}
+
+extern "C" {
+
 int tsp_sparse_attention_f32(int m, int n, int d, int nnz, int replicas, float scale,
                              const int* row_indices, const int* row_offsets,
                              const int* column_indices, const float* q, const float* k,
-                             const float* v, float* out, float* lse_or_null, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+                             const float* v, float* out, float* lse_or_null, void* stream) {
   (void)row_indices;   // rows are taken in order: neighbouring rows share k / v rows in L1
-  if (m < 0 || n < 0 || d < 0 || nnz < 0 || replicas < 0)
-    return invalid("tsp_sparse_attention_f32: negative dimension");
-  if (replicas > 65535) return invalid("tsp_sparse_attention_f32: replicas=%d exceeds 65535", replicas);
-  if (m == 0 || replicas == 0) return TSP_OK;
-  if (!tsp_sparse_attention_supported(n, d))
-    return invalid("tsp_sparse_attention_f32: head dimension %d (n=%d) not supported; use the three-op chain", d, n);
-  if (!row_offsets || !q || !k || !v || !out || (nnz > 0 && !column_indices))
-    return invalid("tsp_sparse_attention_f32: null pointer argument");
-  AttnArgs a;
-  a.m = m; a.n = n; a.d = d; a.nnz = nnz;
-  a.row_offsets = row_offsets; a.column_indices = column_indices;
-  a.q = q; a.k = k; a.v = v; a.out = out; a.lse = lse_or_null; a.scale = scale;
-  if (!attention_rows_applicable(a))
-    return invalid("tsp_sparse_attention_f32: q, k, v and out must be 16-byte aligned");
-  launch_attention_rows(a, replicas, stream);
-  TSP_CHECK_LAUNCH("tsp_sparse_attention_f32");
-  return TSP_OK;
+  return sparse_attention_any<float>("tsp_sparse_attention_f32", m, n, d, nnz, replicas, scale, row_offsets,
+                                     column_indices, q, k, v, out, lse_or_null, stream);
+}
+
+int tsp_sparse_attention_b16(int bf16, int m, int n, int d, int nnz, int replicas, float scale,
+                             const int* row_indices, const int* row_offsets, const int* column_indices,
+                             const void* q, const void* k, const void* v, void* out, float* lse_or_null,
+                             void* stream) {
+  (void)row_indices;
+  return bf16 ? sparse_attention_any<__nv_bfloat16>("tsp_sparse_attention_b16", m, n, d, nnz, replicas, scale,
+                                                    row_offsets, column_indices, q, k, v, out, lse_or_null, stream)
+              : sparse_attention_any<__half>("tsp_sparse_attention_b16", m, n, d, nnz, replicas, scale, row_offsets,
+                                             column_indices, q, k, v, out, lse_or_null, stream);
 }
 
 int tsp_csr_softmax_backward_f32(int m, int nnz, int replicas, float scale, const float* y,
@@ -632,13 +717,14 @@ int tsp_permute_values_b16(int nnz, int replicas, const void* values, const int*
 }  // extern "C"
 
 template <typename T>
-static int spmm_b16(const char* name, int m, int k, int n, int nnz, int replicas, int values_shared,
+static int spmm_b16(const char* name, tsp_plan* plan, int n, int replicas, int values_shared,
                     const int* row_indices, const void* values, const int* value_perm_or_null,
-                    const int* row_offsets, const int* column_indices, const void* dense,
-                    const float* bias_or_null, int relu, void* out, void* stream_) {
+                    const void* dense, const float* bias_or_null, int relu, void* out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
-    return invalid("%s: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", name, m, k, n, nnz, replicas);
+  const int m = plan->m, k = plan->n, nnz = plan->nnz;
+  const int* row_offsets = plan->row_offsets;
+  const int* column_indices = plan->column_indices;
+  if (n < 0 || replicas < 0) return invalid("%s: negative dimension (n=%d replicas=%d)", name, n, replicas);
   if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
   if (m == 0 || n == 0 || replicas == 0) return TSP_OK;
   if (!row_offsets || !out || (nnz > 0 && (!values || !column_indices || !dense)))
@@ -658,17 +744,26 @@ static int spmm_b16(const char* name, int m, int k, int n, int nnz, int replicas
   if (((reinterpret_cast<uintptr_t>(dense) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(values)) & 1u) != 0)
     return invalid("%s: operands must be 2-byte aligned", name);
   if (!spmm_rowsplit_applicable(a)) return invalid("%s: dense operand too large for 32-bit row offsets", name);
-  launch_spmm_rowsplit<T>(a, replicas, stream);
+  const int variant = g_spmm_variant.load();
+  if ((variant == 6 && band_kc<T>(n) != 0 && aligned16(dense) && aligned16(out)) ||
+      (variant == 0 && spmm_band_applicable(a, replicas))) {
+    const int st = try_spmm_band<T>(plan, a, replicas, stream);
+    if (st > 1) return st - 1;
+    if (st == 0) return TSP_OK;
+  }
+  launch_spmm_rowsplit<T>(a, replicas, stream);   // (guarded fallback when a band launch is in front of it)
   TSP_CHECK_LAUNCH(name);
   return TSP_OK;
 }
 
 template <typename T>
-static int sddmm_b16(const char* name, int m, int k, int n, int nnz, int replicas, const int* row_offsets,
-                     const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream_) {
+static int sddmm_b16(const char* name, tsp_plan* plan, int k, int replicas, const void* lhs, const void* rhs,
+                     void* out, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)
-    return invalid("%s: negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", name, m, k, n, nnz, replicas);
+  const int m = plan->m, n = plan->n, nnz = plan->nnz;
+  const int* row_offsets = plan->row_offsets;
+  const int* column_indices = plan->column_indices;
+  if (k < 0 || replicas < 0) return invalid("%s: negative dimension (k=%d replicas=%d)", name, k, replicas);
   if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
   if (nnz == 0 || replicas == 0) return TSP_OK;
   if (!row_offsets || !column_indices || !out || (k > 0 && (!lhs || !rhs)))
@@ -680,7 +775,14 @@ static int sddmm_b16(const char* name, int m, int k, int n, int nnz, int replica
   a.lhs = static_cast<const T*>(lhs);
   a.rhs = static_cast<const T*>(rhs);
   a.out = static_cast<T*>(out);
-  if (g_sddmm_variant.load() != 1 && sddmm_rows_applicable(a)) {
+  const int variant = g_sddmm_variant.load();
+  if ((variant == 6 && band_kc<T>(k) != 0 && aligned16(lhs) && aligned16(rhs)) ||
+      (variant == 0 && sddmm_band_applicable(a, replicas))) {
+    const int st = try_sddmm_band<T>(plan, a, replicas, stream);
+    if (st > 1) return st - 1;
+    if (st == 0) return TSP_OK;
+  }
+  if (variant != 1 && sddmm_rows_applicable(a)) {
     launch_sddmm_rows<T>(a, replicas, stream);
   } else if (k % 8 == 0 && aligned16(lhs) && aligned16(rhs)) {
     if (k <= 64) launch_sddmm_gather<8, 8, T>(a, replicas, stream);
@@ -697,30 +799,56 @@ static int sddmm_b16(const char* name, int m, int k, int n, int nnz, int replica
 
 extern "C" {
 
-int tsp_spmm_f16(int m, int k, int n, int nnz, int replicas, int values_shared, const int* row_indices,
-                 const void* values, const int* value_perm_or_null, const int* row_offsets,
-                 const int* column_indices, const void* dense, const float* bias_or_null, int relu,
-                 void* out, void* stream) {
-  return spmm_b16<__half>("tsp_spmm_f16", m, k, n, nnz, replicas, values_shared, row_indices, values, value_perm_or_null,
-                          row_offsets, column_indices, dense, bias_or_null, relu, out, stream);
+#define TSP_B16_UNPLANNED_SPMM(NAME, TYPE)                                                                     \
+  int NAME(int m, int k, int n, int nnz, int replicas, int values_shared, const int* row_indices,              \
+           const void* values, const int* value_perm_or_null, const int* row_offsets,                          \
+           const int* column_indices, const void* dense, const float* bias_or_null, int relu, void* out,       \
+           void* stream) {                                                                                     \
+    if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)                                                    \
+      return invalid(#NAME ": negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k, n, nnz, replicas); \
+    tsp_plan eph;                                                                                              \
+    ephemeral_plan(&eph, m, k, nnz, row_offsets, column_indices);                                              \
+    const int rc = spmm_b16<TYPE>(#NAME, &eph, n, replicas, values_shared, row_indices, values,                \
+                                  value_perm_or_null, dense, bias_or_null, relu, out, stream);                 \
+    plan_release_ephemeral(&eph, static_cast<cudaStream_t>(stream));                                           \
+    return rc;                                                                                                 \
+  }
+TSP_B16_UNPLANNED_SPMM(tsp_spmm_f16, __half)
+TSP_B16_UNPLANNED_SPMM(tsp_spmm_bf16, __nv_bfloat16)
+
+#define TSP_B16_UNPLANNED_SDDMM(NAME, TYPE)                                                                    \
+  int NAME(int m, int k, int n, int nnz, int replicas, const int* row_indices, const int* row_offsets,         \
+           const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream) {             \
+    (void)row_indices;                                                                                         \
+    if (m < 0 || k < 0 || n < 0 || nnz < 0 || replicas < 0)                                                    \
+      return invalid(#NAME ": negative dimension (m=%d k=%d n=%d nnz=%d replicas=%d)", m, k, n, nnz, replicas); \
+    tsp_plan eph;                                                                                              \
+    ephemeral_plan(&eph, m, n, nnz, row_offsets, column_indices);                                              \
+    const int rc = sddmm_b16<TYPE>(#NAME, &eph, k, replicas, lhs, rhs, out, stream);                           \
+    plan_release_ephemeral(&eph, static_cast<cudaStream_t>(stream));                                           \
+    return rc;                                                                                                 \
+  }
+TSP_B16_UNPLANNED_SDDMM(tsp_sddmm_f16, __half)
+TSP_B16_UNPLANNED_SDDMM(tsp_sddmm_bf16, __nv_bfloat16)
+
+int tsp_plan_spmm_b16(tsp_plan* plan, int bf16, int n, int replicas, int values_shared, const int* row_indices,
+                      const void* values, const int* value_perm_or_null, const void* dense,
+                      const float* bias_or_null, int relu, void* out, void* stream) {
+  if (!plan) return invalid("tsp_plan_spmm_b16: null plan");
+  return bf16 ? spmm_b16<__nv_bfloat16>("tsp_plan_spmm_b16", plan, n, replicas, values_shared, row_indices, values,
+                                        value_perm_or_null, dense, bias_or_null, relu, out, stream)
+              : spmm_b16<__half>("tsp_plan_spmm_b16", plan, n, replicas, values_shared, row_indices, values,
+                                 value_perm_or_null, dense, bias_or_null, relu, out, stream);
 }
-int tsp_spmm_bf16(int m, int k, int n, int nnz, int replicas, int values_shared, const int* row_indices,
-                  const void* values, const int* value_perm_or_null, const int* row_offsets,
-                  const int* column_indices, const void* dense, const float* bias_or_null, int relu,
-                  void* out, void* stream) {
-  return spmm_b16<__nv_bfloat16>("tsp_spmm_bf16", m, k, n, nnz, replicas, values_shared, row_indices, values,
-                                 value_perm_or_null, row_offsets, column_indices, dense, bias_or_null, relu, out, stream);
-}
-int tsp_sddmm_f16(int m, int k, int n, int nnz, int replicas, const int* row_indices, const int* row_offsets,
-                  const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream) {
+
+int tsp_plan_sddmm_b16(tsp_plan* plan, int bf16, int k, int replicas, const int* row_indices, const void* lhs,
+                       const void* rhs, void* out, void* stream) {
   (void)row_indices;
-  return sddmm_b16<__half>("tsp_sddmm_f16", m, k, n, nnz, replicas, row_offsets, column_indices, lhs, rhs, out, stream);
+  if (!plan) return invalid("tsp_plan_sddmm_b16: null plan");
+  return bf16 ? sddmm_b16<__nv_bfloat16>("tsp_plan_sddmm_b16", plan, k, replicas, lhs, rhs, out, stream)
+              : sddmm_b16<__half>("tsp_plan_sddmm_b16", plan, k, replicas, lhs, rhs, out, stream);
 }
-int tsp_sddmm_bf16(int m, int k, int n, int nnz, int replicas, const int* row_indices, const int* row_offsets,
-                   const int* column_indices, const void* lhs, const void* rhs, void* out, void* stream) {
-  (void)row_indices;
-  return sddmm_b16<__nv_bfloat16>("tsp_sddmm_bf16", m, k, n, nnz, replicas, row_offsets, column_indices, lhs, rhs, out, stream);
-}
+
 int tsp_csr_softmax_f16(int m, int nnz, int replicas, float scale, const void* values, const int* row_indices,
                         const int* row_offsets, void* out, void* stream) {
   return softmax_any<__half>("tsp_csr_softmax_f16", m, nnz, replicas, scale, values, row_indices, row_offsets, out, stream);
