@@ -7,9 +7,16 @@ third_party/sputnik/sputnik/spmm/spmm_benchmark.cu.cc:29-33), next to algorithmi
 the fraction of the measured HBM roofline.
 
 A "step" = one pass of the hot path over the workload: for each of the 4 densities one SpMM and
-one SDDMM through the `torch_sputnik` operator API (8 operator calls).  At N > 1 GPUs the path is
-sharded with no collective -- SpMM over dense-operand columns, SDDMM over mask rows -- every rank
-owning a full 4096^3 shard (weak scaling; the global problem is 4096 x 4096 x 4096*N).
+one SDDMM through the `torch_sputnik` operator API (8 operator calls).  At N > 1 GPUs the headline
+`value` is WEAK scaling with no collective: every rank runs its own independent 4096^3 workload
+(so N = 1 equals the single-GPU bench).  The configs that SHARD are measured next to it, in the
+same line, as `scale_cases` -- each with a FIXED global problem split over the N ranks:
+  c2_strong          one global C2 problem, SpMM over dense-operand columns, SDDMM over mask rows
+                     (+ a one-off check that the shards equal the unsharded result)
+  c4_attention_fwd   128 attention replicas split over the ranks (no collective)
+  c3_sparse_linear   sparse linear fwd + wgrad + dgrad over sharded tokens, one overlapped NCCL
+                     all-reduce of the nnz-long value gradient
+  c5_dp_transformer  data-parallel sparse Transformer training step (weak: fixed batch per GPU)
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
@@ -37,14 +44,16 @@ METRIC = "SpMM+SDDMM useful GFLOP/s, 4096^3, density 0.05-0.5 (fp32 CSR)"
 UNIT = "GFLOP/s"
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel behind (op, density), from the
-# `ncu --set full` captures summarised under profiles/ (r01_*_ncu_summary.txt); None = not captured.
-NCU_DRAM_TRAFFIC = {
-    ("spmm", 0.5): 560.6e6,     # profiles/r01_spmm_staged_d050_ncu_summary.txt
-    ("sddmm", 0.5): 1260.6e6,   # profiles/r01_sddmm_tiled2_d050_ncu_summary.txt
-    ("spmm", 0.05): 112.8e6,    # profiles/r01_spmm_gather_d005_ncu_summary.txt
-    ("sddmm", 0.05): 211.5e6,   # profiles/r01_sddmm_sampled_v2_d005_ncu_summary.txt
-}
+def ncu_dram_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel dispatched for (op, density),
+    read from profiles/r02_c2_dram_traffic.json -- written by tools/ncu_traffic.py from one
+    `ncu --set full` capture per dispatched kernel of THIS build (None = not captured)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_c2_dram_traffic.json")) as f:
+            rows = json.load(f)["kernels"]
+        return {(r["op"], float(r["density"])): float(r["dram_bytes"]) for r in rows}
+    except Exception:
+        return {}
 
 _RESULT_OUT = None
 
@@ -80,6 +89,16 @@ def measured_peaks():
         return float(p["hbm_gbs"]), "measured", float(p.get("sm_max_mhz", 1965.0))
     except Exception:
         return 6650.0, "fallback", 1965.0
+
+
+def config_dict(world: int):
+    """The `config` of the result line -- the SAME dict from both arms (ours / reference)."""
+    return {"workload": "C2: SpMM+SDDMM M=N=K=4096 fp32 CSR, density 0.05/0.1/0.25/0.5 "
+                        "(BASELINE.json configs[1]); 8 operator calls per step",
+            "densities": list(DENSITIES),
+            "sharding": "none" if world == 1 else
+                        f"one independent 4096^3 problem per rank x{world} (weak; no collective)",
+            "l2": "inputs larger than L2: 8 cases with distinct buffers (~1.7 GB) cycled per step"}
 
 
 def make_workload(rank: int, dim: int, densities):
@@ -204,8 +223,8 @@ def run_reference_arm(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3 / frac,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "C2: SpMM+SDDMM M=N=K=4096 fp32 CSR, density 0.05/0.1/0.25/0.5",
-                   "densities": list(DENSITIES), "impl": "reference CPU path: dense torch masked matmul"},
+        "config": config_dict(args.gpus),
+        "impl_detail": "reference CPU path: dense torch masked matmul (tests/test_spmm.py:9-10, tests/test_sddmm.py:8-13)",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -344,6 +363,9 @@ def run_ours(args):
     barrier()
     e2e_ms = es.elapsed_time(ee) / e2e_steps
 
+    host_ceiling = host_copy_ceiling(torch, dist, dev, world, barrier)
+    scale = scale_cases(args, torch, dist, ops, dev, world, rank, cases, barrier)
+
     # ---- max over ranks ---------------------------------------------------------------------
     times = torch.tensor([ms_total, e2e_ms, e2e_serial_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -375,31 +397,28 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2: SpMM+SDDMM M=N=K=4096 fp32 CSR, density 0.05/0.1/0.25/0.5 "
-                                   "(BASELINE.json configs[1]); 8 operator calls per step",
-                       "densities": list(DENSITIES),
-                       "sharding": "none" if world == 1 else
-                                   f"SpMM over dense columns, SDDMM over mask rows; one 4096^3 shard per rank x{world}",
-                       "l2": "inputs larger than L2: 8 cases with distinct buffers (~1.7 GB) cycled per step",
-                       "api": "torch_sputnik.spmm / torch_sputnik.sddmm"},
+            "config": config_dict(world),
+            "impl_detail": "torch_sputnik.spmm / torch_sputnik.sddmm (in-tree sm_100a extension)",
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms, "steps": e2e_steps,
                     "api": "torch_sputnik_b200.host.HostPipeline (pinned host operands; upload / kernel / "
                            "download streams overlapped across calls)",
                     "serial_ms_per_step": e2e_serial_ms, "numa_bound_cores": len(numa_cores),
-                    "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1)},
+                    "pcie_gbs": round((h2d + d2h) / (e2e_ms * 1e-3) / 1e9, 1),
+                    "host_copy_ceiling": host_ceiling},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": f"{top['op']} d={top['density']}",
                          "achieved": top["algorithmic_gbs"], "peak": peak, "peak_kind": peak_kind,
                          "unit": "GB/s", "frac": top["hbm_frac"],
-                         "traffic": NCU_DRAM_TRAFFIC.get((top["op"], top["density"])),
+                         "traffic": ncu_dram_traffic().get((top["op"], float(top["density"]))),
                          "algorithmic_bytes": top["algorithmic_bytes"],
                          "fp32_frac": top["fp32_frac"], "avg_launch_ms": top["ms"],
                          "note": "unstructured CSR at these shapes is bound by shared-memory/L1 gather "
                                  "bandwidth and fp32 issue, not HBM (DESIGN.md); fp32_frac is vs "
                                  f"{fp32_peak:.1f} TFLOP/s non-tensor peak"},
             "cases": table,
+            "scale_cases": scale,
         }
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg(cases, torch)
@@ -412,6 +431,216 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def host_copy_ceiling(torch, dist, dev, world, barrier):
+    """What the box's host memory system can move with ALL ranks copying at once: pinned 256 MB
+    host -> device and device -> host, concurrently on two streams, max time over ranks.  This is the
+    ceiling of the `e2e` leg (926 MB up + 329 MB down per step and rank): at N = 8 the eight uploads
+    share one socket's memory controllers, which bounds e2e scaling whatever the kernels do."""
+    try:
+        n = 64 * 1024 * 1024   # fp32 elements = 256 MB
+        h_up, h_dn = torch.empty(n, dtype=torch.float32).pin_memory(), torch.empty(n, dtype=torch.float32).pin_memory()
+        d_up, d_dn = torch.empty(n, device=dev), torch.empty(n, device=dev)
+        s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        reps = 4
+
+        def run():
+            with torch.cuda.stream(s1):
+                for _ in range(reps):
+                    d_up.copy_(h_up, non_blocking=True)
+            with torch.cuda.stream(s2):
+                for _ in range(reps):
+                    h_dn.copy_(d_dn, non_blocking=True)
+        run()
+        torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        run()
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        per_rank = 2 * reps * n * 4 / float(dt) / 1e9
+        return {"gbs_per_rank_both_directions": round(per_rank, 1), "gbs_aggregate": round(per_rank * world, 1),
+                "how": f"{world} rank(s) copying 256 MB pinned buffers H2D and D2H concurrently, x{reps}, max over ranks"}
+    except Exception as exc:   # measurement aid only
+        return {"unavailable": repr(exc)}
+
+
+def _timed(torch, dist, dev, world, barrier, fn, reps, warm=2):
+    """ms per call of fn(): CUDA events on the current stream, barrier on both sides, max over ranks."""
+    for _ in range(warm):
+        fn()
+    barrier()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(reps):
+        fn()
+    e.record()
+    barrier()
+    ms = torch.tensor([s.elapsed_time(e) / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms)
+
+
+def scale_cases(args, torch, dist, ops, dev, world, rank, cases, barrier):
+    """The configs of BASELINE.json that SHARD, each as ms per step at this N with a
+    FIXED global problem (strong scaling) unless noted, so 1 -> N speed-ups follow from the driver's
+    N = 1, 2, 4, 8 lines.  Outside the headline's timed region; a failing case reports its error
+    instead of taking the headline down."""
+    from torch_sputnik_b200 import dist as tdist
+    from oracle.csr import random_csr      # input generator only
+    out = {}
+    reps = max(3, min(args.steps, 10))
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+    # -- C2, ONE global 4096^3 problem: SpMM over dense-operand columns, SDDMM over nnz-balanced mask rows
+    try:
+        glob = cases if rank == 0 else make_workload(0, DIM, DENSITIES)
+        work, identical, within = [], True, True
+        for c in glob:
+            a = c["csr"]
+            d = c["devt"] if "devt" in c else {k: t(v) for k, v in dict(
+                values=a.values, row_indices=a.row_indices, row_offsets=a.row_offsets,
+                column_indices=a.column_indices, dense=c["dense"], lhs=c["lhs"], rhs=c["rhs"]).items()}
+            cols = tdist.shard_columns(DIM, world, rank)
+            dense_l = d["dense"][:, cols].contiguous()
+            sh = tdist.shard_rows_by_nnz(d["row_offsets"], world)[rank]
+            m_l, ri_l, ro_l, ci_l = tdist.slice_csr_rows(sh, d["row_offsets"], d["column_indices"])
+            lhs_l = d["lhs"][sh.row_begin:sh.row_end].contiguous()
+            work.append((d, dense_l, m_l, ri_l, ro_l, ci_l, lhs_l))
+            if world > 1:      # one-off: the shards reassemble to the unsharded result
+                full = ops.spmm(DIM, DIM, d["values"], d["row_indices"], d["row_offsets"], d["column_indices"], d["dense"])
+                mine = ops.spmm(DIM, DIM, d["values"], d["row_indices"], d["row_offsets"], d["column_indices"], dense_l)
+                identical &= bool(torch.equal(full[:, cols], mine))
+                within &= bool(torch.allclose(full[:, cols], mine, rtol=1e-4, atol=1e-3))
+                fulls = ops.sddmm(DIM, DIM, d["row_indices"], d["row_offsets"], d["column_indices"], d["lhs"], d["rhs"])
+                mines = ops.sddmm(m_l, DIM, ri_l, ro_l, ci_l, lhs_l, d["rhs"])
+                identical &= bool(torch.equal(fulls[sh.nnz_begin:sh.nnz_end], mines))
+                within &= bool(torch.allclose(fulls[sh.nnz_begin:sh.nnz_end], mines, rtol=1e-4, atol=1e-3))
+                del full, mine, fulls, mines
+
+        def c2_step():
+            for d, dense_l, m_l, ri_l, ro_l, ci_l, lhs_l in work:
+                ops.spmm(DIM, DIM, d["values"], d["row_indices"], d["row_offsets"], d["column_indices"], dense_l)
+                ops.sddmm(m_l, DIM, ri_l, ro_l, ci_l, lhs_l, d["rhs"])
+        ms = _timed(torch, dist, dev, world, barrier, c2_step, reps)
+        flags = torch.tensor([int(identical), int(within)], device=dev)
+        if world > 1:
+            dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+        out["c2_strong"] = {"ms_per_step": round(ms, 4), "scaling": "strong",
+                            "what": "ONE global 4096^3 problem, 4 densities: SpMM sharded over dense-operand columns, "
+                                    "SDDMM over nnz-balanced mask rows; no collective",
+                            "useful_gflops": round(useful_flops(glob, DIM) / (ms * 1e-3) / 1e9, 1),
+                            "shards_bit_identical_to_unsharded": bool(flags[0]) if world > 1 else None,
+                            "shards_within_tolerance": bool(flags[1]) if world > 1 else None}
+        del work, glob
+    except Exception as exc:
+        out["c2_strong"] = {"error": repr(exc)}
+
+    # -- C4: attention forward chain, R = 128 replicas of one 4096^2 mask (90 % sparse), head dim 64
+    try:
+        s_len, hd, replicas = 4096, 64, 128
+        rs = tdist.shard_replicas(replicas, world, rank)
+        r_l = rs.stop - rs.start
+        a = random_csr(s_len, s_len, 0.1, seed=0, values="pm1", round_to=4)
+        ri, ro, ci = t(a.row_indices), t(a.row_offsets), t(a.column_indices)
+        g = torch.Generator(device=dev).manual_seed(10 + rank)
+        q, k, v = (torch.rand((r_l, s_len, hd), generator=g, device=dev) * 2 - 1 for _ in range(3))
+
+        def c4_step(q=q, k=k, v=v):
+            sc = ops.sddmm(s_len, s_len, ri, ro, ci, q, k)
+            pr = ops.sparse_softmax_scaled(sc, ri, ro, ci, 1.0 / 8.0)
+            return ops.spmm(s_len, s_len, pr, ri, ro, ci, v)
+        ms = _timed(torch, dist, dev, world, barrier, c4_step, reps)
+        qh, kh, vh = q.half(), k.half(), v.half()
+        ms16 = _timed(torch, dist, dev, world, barrier, lambda: c4_step(qh, kh, vh), reps)
+        out["c4_attention_fwd"] = {"ms_per_step": round(ms, 4), "ms_per_step_f16": round(ms16, 4), "scaling": "strong",
+                                   "what": "sddmm -> csr softmax (scale fused) -> spmm, 128 replicas (batch 8 x 16 heads) "
+                                           "x seq 4096 x head dim 64, mask 90 % sparse; replicas sharded, topology replicated; "
+                                           "no collective", "replicas_per_gpu": r_l}
+        del q, k, v, qh, kh, vh
+    except Exception as exc:
+        out["c4_attention_fwd"] = {"error": repr(exc)}
+
+    # -- C3: sparse linear 4096 x 4096 at 90 % sparsity, 8192 tokens as [16, 512]: forward, weight gradient
+    #    (replica-summed SDDMM into the gradient bucket, all-reduced over ranks on a side stream while the
+    #    data gradient runs), data gradient.  Tokens (batch entries) sharded.
+    try:
+        m = k = 4096
+        tokens, batch = 512, 16
+        b0, b1 = tdist.shard_range(batch, world, rank)
+        b_l = max(1, b1 - b0)
+        a = random_csr(m, k, 0.1, seed=0, values="pm1")
+        ri, ro, ci = t(a.row_indices), t(a.row_offsets), t(a.column_indices)
+        w = torch.nn.Parameter(t(a.values))
+        bucket = tdist.ValueGradBucket([w])
+        g = torch.Generator(device=dev).manual_seed(20 + rank)
+        x = torch.rand((b_l, k, tokens), generator=g, device=dev) * 2 - 1     # x^T: [B, in, S]
+        dy = torch.rand((b_l, m, tokens), generator=g, device=dev) * 2 - 1    # [B, out, S]
+        rot, cit, perm, rit = ops.transposed_topology(m, k, ro, ci)
+
+        def c3_step():
+            ops.left_spmm(m, k, w.detach(), ri, ro, ci, x)                                   # forward
+            bucket.flat.copy_(ops.sddmm_reduce(m, k, ri, ro, ci, dy, x))                     # weight gradient
+            bucket.all_reduce()                                                              # side stream
+            ops.left_spmm(k, m, ops.permute_values(w.detach(), perm), rit, rot, cit, dy)     # data gradient
+            bucket.wait()
+        ms = _timed(torch, dist, dev, world, barrier, c3_step, reps)
+        out["c3_sparse_linear"] = {"ms_per_step": round(ms, 4), "scaling": "strong",
+                                   "what": "left_spmm forward + sddmm_reduce weight gradient + transposed left_spmm data "
+                                           "gradient, W 4096x4096 at 90 % sparsity, 8192 tokens ([16, 512]) sharded over "
+                                           "batch entries; ONE NCCL all-reduce of the nnz-long value gradient per step, "
+                                           "overlapped with the data gradient", "batch_per_gpu": b_l,
+                                   "allreduce_bytes": int(bucket.nbytes) if world > 1 else 0}
+        del x, dy, bucket, w
+    except Exception as exc:
+        out["c3_sparse_linear"] = {"error": repr(exc)}
+
+    # -- C5: data-parallel training step of the sparse Transformer (weak: 4 sequences of 512 per GPU)
+    try:
+        from torch_sputnik_b200.modules.transformer import SparseTransformer
+        torch.manual_seed(0)
+        vocab, bsz, seq = 1000, 4, 512
+        model = SparseTransformer(6, 512, 8, 2048, seq, vocab, device=dev).to(dev)
+        model.setup_sparse()
+        sparse = tdist.sparse_value_parameters(model)
+        ids = {id(p) for p in sparse}
+        dense = [p for p in model.parameters() if p.requires_grad and id(p) not in ids]
+        tdist.broadcast_parameters(sparse + dense)
+        b_sparse, b_dense = tdist.ValueGradBucket(sparse), tdist.ValueGradBucket(dense)
+        gen = torch.Generator(device="cpu").manual_seed(100 + rank)
+        tok = torch.randint(0, vocab, (bsz, seq), generator=gen).to(dev)
+        tgt = torch.randint(0, vocab, (bsz, seq), generator=gen).to(dev)
+        loss_fn = torch.nn.CrossEntropyLoss()
+
+        def c5_step():
+            b_sparse.zero_()
+            b_dense.zero_()
+            loss = loss_fn(model(tok).reshape(-1, vocab), tgt.reshape(-1))
+            loss.backward()
+            b_sparse.all_reduce()
+            b_dense.all_reduce()
+            b_sparse.wait()
+            b_dense.wait()
+            with torch.no_grad():
+                for p in sparse + dense:
+                    p.add_(p.grad, alpha=-1e-2)
+        ms = _timed(torch, dist, dev, world, barrier, c5_step, reps, warm=3)
+        out["c5_dp_transformer"] = {"ms_per_step": round(ms, 4), "scaling": "weak",
+                                    "tokens_per_s": round(world * bsz * seq / (ms * 1e-3), 1),
+                                    "what": "sparse Transformer (6 layers, hidden 512, 8 heads, ffn 2048, seq 512; 90 %-sparse "
+                                            "linear layers + shared-mask sparse attention), 4 sequences per GPU, eager "
+                                            "launches; one NCCL all-reduce of the nnz-long value gradients + one of the "
+                                            "small dense parameters per step",
+                                    "allreduce_bytes": int(b_sparse.nbytes + b_dense.nbytes) if world > 1 else 0}
+        del model, b_sparse, b_dense
+    except Exception as exc:
+        out["c5_dp_transformer"] = {"error": repr(exc)}
+    torch.cuda.empty_cache()
+    return out
 
 
 def cpu_baseline_leg(cases, torch):
@@ -451,15 +680,16 @@ def reference_kernel_leg(cases, dev, torch):
                    ("sddmm", lambda: ref_gpu.sddmm(DIM, DIM, d["row_indices"], d["row_offsets"],
                                                    d["column_indices"], d["lhs"], d["rhs"])))
             for op, fn in fns:
-                fn()
+                for _ in range(2):
+                    fn()
                 torch.cuda.synchronize()
                 s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 s.record()
-                for _ in range(3):
+                for _ in range(10):
                     fn()
                 e.record()
                 torch.cuda.synchronize()
-                ms = s.elapsed_time(e) / 3
+                ms = s.elapsed_time(e) / 10
                 rows.append({"op": op, "density": c["density"], "ms": round(ms, 4),
                              "useful_gflops": round(2.0 * nnz * DIM / (ms * 1e-3) / 1e9, 1)})
                 total_ms += ms

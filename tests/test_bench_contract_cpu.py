@@ -30,6 +30,9 @@ def test_reference_arm_prints_one_json_line_with_the_contract_keys():
                 "data", "config", "cpu_baseline", "e2e"):
         assert key in d, key
     assert "workload" in d["config"] and "model" not in d["config"]
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["config"] == bench.config_dict(1)          # the SAME dict the GPU arm emits (vs_reference.same_config)
     assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
     assert d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}

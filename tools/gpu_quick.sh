@@ -3,4 +3,4 @@ set -u
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
 tail -8 gpurun_out/pytest_gpu.log
-timeout 600 python tools/ab_band.py 2>&1 | tee gpurun_out/ab_band.jsonl
+timeout 600 python tools/ab_band.py 2>&1 | tee gpurun_out/ab_band.jsonl | cut -c1-400

@@ -18,7 +18,7 @@
 //  * a CTA is 16 consecutive rows: with ascending columns they sweep the rhs rows in near
 //    lockstep, so the rows they share are L1 hits ("implicit banding").
 //
-// Arithmetic: per lane fp32 FMA in ascending k inside its chunks, then a fp32 tree over the 8
+// Arithmetic: per lane two fp32 FMA chains (even / odd k) in ascending k inside its chunks, their sum, then a fp32 tree over the 8
 // lanes -- the shape of the reference's (all_reduce.h:61-80), a different association.
 // Works for any column order (no sortedness assumption).  Needs k % 32 == 0, k <= 128,
 // 16-byte aligned operands and n * k * 4 < 2^31.
@@ -53,16 +53,26 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT
   float lv[KC][E];
 #pragma unroll
   for (int cc = 0; cc < KC; ++cc) load_elems<T, E>(lv[cc], lrow + cc * 8 * E);
+  // Even and odd elements of the lane's chunks are summed separately as one packed fma.rn.f32x2
+  // chain (half the issue slots), then added -- the SAME association as sddmm_band (band.cuh), so the
+  // two kernels the heuristic chooses between for a short inner dimension agree bit for bit.
   auto dot_row = [&](const unsigned o) {   // o: rhs row offset in 16-byte units
-    float s = 0.f;
+    float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int cc = 0; cc < KC; ++cc) {
       float x[E];
       load_elems<T, E>(x, rbase + ((size_t)o + cc * 8) * E);
 #pragma unroll
-      for (int e = 0; e < E; ++e) s = fmaf(lv[cc][e], x[e], s);
+      for (int e = 0; e < E; e += 2) {
+        if constexpr (sizeof(T) == 4) {
+          ffma2(s0, s1, lv[cc][e], lv[cc][e + 1], x[e], x[e + 1]);
+        } else {   // 16-bit storage: the unpacked pairs are not register-adjacent, packing them costs more than it saves (2.08 vs 1.90 ms at C4)
+          s0 = fmaf(lv[cc][e], x[e], s0);
+          s1 = fmaf(lv[cc][e + 1], x[e + 1], s1);
+        }
+      }
     }
-    return s;
+    return s0 + s1;
   };
 
   for (int p = beg; p < end; p += 32) {
