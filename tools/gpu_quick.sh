@@ -1,6 +1,6 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
-tail -8 gpurun_out/pytest_gpu.log
-timeout 600 python tools/ab_band.py 2>&1 | tee gpurun_out/ab_band.jsonl | cut -c1-400
+for scb in 2 4 16; do echo "scb=$scb"; TSP_SPMM_SCB=$scb python tools/prof_case.py spmm 0.5 5; TSP_SPMM_SCB=$scb python tools/prof_case.py spmm 0.25 5; done
+timeout 300 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_sector_hit_rate.pct --clock-control none -k regex:spmm_staged -s 2 -c 1 python tools/prof_case.py spmm 0.5 3 2>&1 | grep -E "dram__|gpu__time|lts__"
+timeout 900 python -m pytest tests/test_gpu_spmm.py tests/test_gpu_sddmm.py tests/test_gpu_plans.py tests/test_gpu_golden.py -q 2>&1 | tail -2

@@ -186,6 +186,23 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const void* tmap, in
       : "memory");
 }
 
+// L2-aware rasterisation of a 2-D grid of tiles (rows x cols) walked as a 1-D sequence: tiles are
+// numbered band by band (srb tile rows per band), inside a band group by group (scb tile columns
+// per group), inside a group row-major.  With srb * scb ~ the number of CTAs resident at once, the
+// CTAs in flight share ONE group: srb tile rows of the left operand + scb tile columns of the right
+// operand -- a footprint sized to stay in L2 -- and successive groups of a band reuse its rows.
+__device__ __forceinline__ void raster_tile(int t, int rows, int cols, int srb, int scb, int& r, int& c) {
+  const int band_full = srb * cols;
+  const int b = t / band_full, tb = t - b * band_full;
+  const int band_rows = min(srb, rows - b * srb);
+  const int group_full = band_rows * scb;
+  const int g = tb / group_full, tg = tb - g * group_full;
+  const int w = min(scb, cols - g * scb);
+  const int rl = tg / w;
+  r = b * srb + rl;
+  c = g * scb + (tg - rl * w);
+}
+
 // ---- storage types: fp32, or fp16 / bf16 storage with fp32 arithmetic (the
 // reference's half SpMM, cuda_spmm.cu.cc:511-570, keeps fp32 accumulators the same way) -------------
 template <typename T>

@@ -257,10 +257,27 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
   const int rep = blockIdx.y;
   const int ksteps1 = (a.k + BK - 1) / BK;                                   // k-steps of one replica
   const int ksteps = a.reduce_reps > 0 ? ksteps1 * a.reduce_reps : ksteps1;   // k-steps per tile
-  const int t0 = blockIdx.x * tiles_per_cta;
-  const int t1 = min(total_tiles, t0 + tiles_per_cta);
-  if (t0 >= t1) return;
-  const int Q = (t1 - t0) * ksteps;
+  // Tiles are dealt round-robin: CTA i takes tiles i, i + G, i + 2G, ... (G = gridDim.x) of the
+  // rasterised sequence (raster_tile: bands of 16 row blocks, groups of 16 column blocks -- 256 tiles,
+  // about one wave of CTAs).  CTAs advance roughly in step, so the CTAs in flight share 16 x 128 lhs
+  // rows + 16 x 64 rhs rows (48 MB at k = 4096), the groups of a band reuse its lhs rows from L2, and
+  // every operand byte comes from HBM about twice -- against every CTA streaming a private row block and
+  // all of rhs at once when each owned a contiguous run of tiles (dram__bytes 1261 MB for 201 MB of
+  // operands at density 0.5, profiles/r01_sddmm_tiled2_d050_ncu_summary.txt).
+  // (The CTA's tile coordinates are worked out ONCE, by its first threads, into shared memory: the
+  // kernel sits at 255 registers and the raster arithmetic inside the tile loop spilled.)
+  constexpr int SRB = 16, SCB = 16, kMaxTilesPerCta = 64;
+  __shared__ int s_tile[kMaxTilesPerCta];
+  (void)tiles_per_cta;
+  const int G = gridDim.x;
+  const int ntiles = (int)blockIdx.x < total_tiles ? (total_tiles - (int)blockIdx.x + G - 1) / G : 0;
+  if (ntiles == 0) return;
+  const int Q = ntiles * ksteps;
+  if ((int)threadIdx.x < min(ntiles, kMaxTilesPerCta)) {
+    int rb, cb;
+    raster_tile((int)blockIdx.x + (int)threadIdx.x * G, total_tiles / col_blocks, col_blocks, SRB, SCB, rb, cb);
+    s_tile[threadIdx.x] = (rb << 16) | cb;
+  }
 
   if (tid == 0) {
 #pragma unroll
@@ -278,9 +295,10 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
     const int st = q % STAGES, use = q / STAGES;
     if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
     if (lane == 0) {
-      const int t = t0 + q / ksteps, kq = q % ksteps;
+      const int kq = q % ksteps;
       const int ks = kq % ksteps1, rr = a.reduce_reps > 0 ? kq / ksteps1 : rep;
-      const int rb = t / col_blocks, cb = t % col_blocks;
+      const int packed = s_tile[q / ksteps];
+      const int rb = packed >> 16, cb = packed & 0xffff;
       float* const sa = ring + st * C::kStageFloats;
       mbar_arrive_expect_tx(full + st, C::kStageBytes);
       tma_load_3d(sa, &tm_lhs, ks * BK, rb * BM, rr, full + st);
@@ -301,8 +319,8 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
   const int xa = ty, xb0 = tx, xb1 = 4 + tx;
 
   int q = 0;
-  for (int t = t0; t < t1; ++t) {
-    const int rb = t / col_blocks, cb = t % col_blocks;
+  for (int ti = 0; ti < ntiles; ++ti) {
+    const int rb = s_tile[ti] >> 16, cb = s_tile[ti] & 0xffff;
     unsigned long long my_mask = 0ull;
     int my_base = 0;
     if (rb * BM + tid < a.m) {   // THREADS == BM
@@ -458,6 +476,7 @@ inline int launch_sddmm_tiled(const SddmmArgs& a, int replicas, cudaStream_t str
   const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;
   int per_cta = (int)((total * grid_reps + slots - 1) / slots);
   per_cta = per_cta < 1 ? 1 : (per_cta > col_blocks ? col_blocks : per_cta);
+  if (per_cta > 64) per_cta = 64;   // sddmm_tiled2_kernel keeps its tile list in a 64-entry shared array
   const int ctas = (int)((total + per_cta - 1) / per_cta);
   const size_t entries = (size_t)a.m * col_blocks;
   const unsigned long long* masks = static_cast<const unsigned long long*>(view);

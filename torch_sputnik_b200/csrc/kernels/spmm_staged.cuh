@@ -116,7 +116,8 @@ __device__ __noinline__ void spmm_staged_redo_row(const float* __restrict__ dens
 
 template <class Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS, (Cfg::kSmemBytes <= 110 * 1024) ? 2 : 1)
-spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
+spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard, const int row_blocks, const int col_tiles, const int srb,
+                   const int scb) {
   constexpr int NV4 = Cfg::NV4, NT = Cfg::NT, G = Cfg::G, KS = Cfg::KS, STAGES = Cfg::STAGES,
                 WARPS = Cfg::WARPS, U = Cfg::U, R = Cfg::R, LPR = Cfg::LPR;
   if (staged_declines(guard)) return;  // gather kernel takes over
@@ -129,7 +130,24 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = a.n, k = a.k;
-  const int n0 = blockIdx.y * NT;
+  // The (row block, column tile) pairs are walked in the L2-aware order of raster_tile: the CTAs
+  // resident together (srb x scb of them, one wave) share srb row blocks of A and scb column tiles of
+  // the dense operand (16 MB at k = 4096, scb = 4), and the column groups of a band reuse its rows of A
+  // from L2.  With row blocks as the fast grid dimension each column-tile pass re-streamed all of A and
+  // B came from HBM once per row block wave (dram__bytes 561 MB for 201 MB of operands at density 0.5,
+  // profiles/r01_spmm_staged_d050_ncu_summary.txt).
+  // (Worked out once by thread 0 into shared memory and re-read where needed: the kernel sits at its
+  // register budget, and two more live registers across the slab loop spilled -- 3.39 vs 3.15 ms.)
+  __shared__ int s_where[2];
+  if (threadIdx.x == 0) {
+    int rb, nt;
+    raster_tile((int)blockIdx.x, row_blocks, col_tiles, srb, scb, rb, nt);
+    s_where[0] = rb;
+    s_where[1] = nt * NT;
+  }
+  const volatile int* const where = s_where;
+#define row_block (where[0])
+#define n0 (where[1])
   const int rep = blockIdx.z;
   const int nslabs = (k + KS - 1) / KS;
 
@@ -171,7 +189,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   int pos[G], endp[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    const int item = blockIdx.x * Cfg::RB + (warp * G + g) * R + r_lane;
+    const int item = row_block * Cfg::RB + (warp * G + g) * R + r_lane;
     pos[g] = endp[g] = 0;
     if (item < a.m) {
       const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
@@ -333,7 +351,7 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
   for (int g = 0; g < G; ++g)
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      const int item = blockIdx.x * Cfg::RB + (warp * G + g) * R + r;
+      const int item = row_block * Cfg::RB + (warp * G + g) * R + r;
       if (item >= a.m) continue;
       const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
       // x - x is 0 for finite x and NaN otherwise; one sum per row finds any non-finite accumulator
@@ -367,6 +385,9 @@ spmm_staged_kernel(const SpmmArgs a, const StagedGuard guard) {
     }
 }
 
+#undef row_block
+#undef n0
+
 // ------------------------------------------------------------------------------------ host
 inline bool spmm_staged_applicable(const SpmmArgs& a, int replicas) {
   if (a.value_perm != nullptr) return false;   // the staged kernel sits at its register budget; permuted values go through the gather kernel
@@ -376,6 +397,8 @@ inline bool spmm_staged_applicable(const SpmmArgs& a, int replicas) {
   // Small problems are launch-bound; staging cannot pay for its prologue there.
   return 2.0 * a.nnz * a.n * replicas >= 5.0e7;
 }
+
+extern std::atomic<int> g_spmm_scb;
 
 template <class Cfg>
 inline int launch_spmm_staged_cfg(const SpmmArgs& a, int replicas, const StagedGuard& guard,
@@ -390,8 +413,14 @@ inline int launch_spmm_staged_cfg(const SpmmArgs& a, int replicas, const StagedG
     if (e != cudaSuccess) return cuda_fail(e, "tsp_spmm_f32 (staged smem attribute)");
     configured[dev] = true;
   }
-  dim3 grid(ceil_div(a.m, Cfg::RB), ceil_div(a.n, Cfg::NT), replicas);
-  spmm_staged_kernel<Cfg><<<grid, Cfg::THREADS, Cfg::kSmemBytes, stream>>>(a, guard);
+  const int row_blocks = ceil_div(a.m, Cfg::RB), col_tiles = ceil_div(a.n, Cfg::NT);
+  // one wave of CTAs per (band, column group): scb column tiles x srb row blocks
+  const int resident = sm_count() * (Cfg::kSmemBytes <= 110 * 1024 ? 2 : 1);
+  const int want_scb = g_spmm_scb.load() > 0 ? g_spmm_scb.load() : 4;   // benchmark knob "spmm_scb"
+  const int scb = col_tiles < want_scb ? col_tiles : want_scb;
+  const int srb = (resident + scb - 1) / scb;
+  dim3 grid((unsigned)((long long)row_blocks * col_tiles), 1, replicas);
+  spmm_staged_kernel<Cfg><<<grid, Cfg::THREADS, Cfg::kSmemBytes, stream>>>(a, guard, row_blocks, col_tiles, srb, scb);
   return 0;
 }
 

@@ -29,6 +29,7 @@ std::atomic<int> g_spmm_warps{0};
 std::atomic<int> g_sddmm_warps{0};
 std::atomic<int> g_attn_warps{0};
 std::atomic<int> g_band_warps{0};
+std::atomic<int> g_spmm_scb{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_spmm_rowsplit_max_n{0};   // fp32 operands up to this many columns take spmm_rowsplit
 static std::atomic<int> g_sddmm_bn{0};
@@ -79,6 +80,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm_rowsplit_max_n") == 0) return g_spmm_rowsplit_max_n.exchange(variant);
   if (op && strcmp(op, "spmm_warps") == 0) return g_spmm_warps.exchange(variant);
   if (op && strcmp(op, "sddmm_warps") == 0) return g_sddmm_warps.exchange(variant);
+  if (op && strcmp(op, "spmm_scb") == 0) return g_spmm_scb.exchange(variant);
   if (op && strcmp(op, "band_warps") == 0) return g_band_warps.exchange(variant);
   if (op && strcmp(op, "attn_warps") == 0) return g_attn_warps.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
