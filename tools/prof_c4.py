@@ -1,5 +1,5 @@
 """One op at the attention shape (s=4096, d=64, 90 % sparse mask), few replicas -- for ncu captures.
-usage: python tools/prof_c4.py spmm|sddmm|attn [REPLICAS] [REPS]   (TSP_VARIANT forces a kernel variant)"""
+usage: python tools/prof_c4.py spmm|sddmm|softmax|attn [REPLICAS] [REPS]   (TSP_VARIANT forces a kernel variant, TSP_DTYPE=f16)"""
 import os
 import sys
 
@@ -27,15 +27,29 @@ t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev)
 ri, ro, ci = t(a.row_indices), t(a.row_offsets), t(a.column_indices)
 q, k, v = (torch.rand((R, s, d), device=dev) * 2 - 1 for _ in range(3))
 p = torch.rand((R, a.nnz), device=dev)
-ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
-ev[0].record()
-for i in range(reps):
+if os.environ.get("TSP_DTYPE") == "f16":
+    q, k, v, p = q.half(), k.half(), v.half(), p.half()
+
+
+def call():
     if op == "spmm":
         ops.spmm(s, s, p, ri, ro, ci, v)
     elif op == "attn":
         ops.sparse_attention(s, s, ri, ro, ci, q, k, v, 0.125)
+    elif op == "softmax":
+        ops.sparse_softmax_scaled(p, ri, ro, ci, 0.125)
     else:
         ops.sddmm(s, s, ri, ro, ci, q, k)
+
+
+call()
+torch.cuda.synchronize()
+torch.cuda.cudart().cudaProfilerStart()      # `ncu --profile-from-start off`: steady-state launches only
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+ev[0].record()
+for i in range(reps):
+    call()
     ev[i + 1].record()
 torch.cuda.synchronize()
+torch.cuda.cudart().cudaProfilerStop()
 print(op, "R=%d" % R, [round(ev[i].elapsed_time(ev[i + 1]), 4) for i in range(reps)], "ms")
