@@ -1,14 +1,16 @@
 #!/bin/bash
-# usage: gpu_multi.sh N   -- the sharded paths on N GPUs of one box (run under `gpurun --gpus N`)
-# Every command has a SHORT timeout: an 8-GPU call is charged 8x, and one process that does not exit (a hang in NCCL
-# teardown once cost 74 GPU-minutes) must not hold the box until the call limit.
+# Multi-GPU pass on one box: bench.py (headline + scale_cases) at N ranks, then the C5 training step under a CUDA graph.
 set -u
-N=${1:-2}
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
-nvidia-smi -L > gpurun_out/smi_n$N.txt
-timeout 240 $TR bench.py --gpus $N --steps 5 --warmup 3 --no-cpu-baseline --no-ref-kernel > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"; tail -2 gpurun_out/bench_n$N.err
-timeout 240 $TR tools/bench_configs.py --config c4 > gpurun_out/configs_c4_n$N.jsonl 2> gpurun_out/configs_c4_n$N.err; echo "c4 rc=$?"; tail -2 gpurun_out/configs_c4_n$N.err
-timeout 240 $TR tools/bench_configs.py --config c3 > gpurun_out/configs_c3_n$N.jsonl 2> gpurun_out/configs_c3_n$N.err; echo "c3 rc=$?"; tail -2 gpurun_out/configs_c3_n$N.err
-timeout 120 $TR tools/train_dp_transformer.py --steps 10 > gpurun_out/c5_n$N.json 2> gpurun_out/c5_n$N.err; echo "c5 rc=$?"; tail -2 gpurun_out/c5_n$N.err
-cat gpurun_out/c5_n$N.json
+N=${1:-8}
+nvidia-smi topo -m > gpurun_out/r02_topo_n$N.txt 2>&1
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/r02_bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"
+tail -c 600 gpurun_out/bench_n$N.err
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/train_dp_transformer.py --graph 1 --steps 10 > gpurun_out/r02_c5_graph_n$N.json 2> gpurun_out/c5_n$N.err; echo "c5 rc=$?"
+cat gpurun_out/r02_c5_graph_n$N.json
+python - $N <<'PY'
+import json,sys
+d=json.load(open(f'gpurun_out/r02_bench_n{sys.argv[1]}.json'))
+print(d['n_gpus'], d['value'], d['ms_per_step'], d['gpu_launches'], d['e2e']['value'], d['e2e']['ms_per_step'], d['e2e']['host_copy_ceiling'])
+print(json.dumps({k:{kk:vv for kk,vv in v.items() if kk!='what'} for k,v in d['scale_cases'].items()}, indent=1))
+PY
