@@ -1,6 +1,9 @@
 #!/bin/bash
 set -u
-mkdir -p gpurun_out
-for scb in 2 4 16; do echo "scb=$scb"; TSP_SPMM_SCB=$scb python tools/prof_case.py spmm 0.5 5; TSP_SPMM_SCB=$scb python tools/prof_case.py spmm 0.25 5; done
-timeout 300 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_sector_hit_rate.pct --clock-control none -k regex:spmm_staged -s 2 -c 1 python tools/prof_case.py spmm 0.5 3 2>&1 | grep -E "dram__|gpu__time|lts__"
-timeout 900 python -m pytest tests/test_gpu_spmm.py tests/test_gpu_sddmm.py tests/test_gpu_plans.py tests/test_gpu_golden.py -q 2>&1 | tail -2
+for d in 0.05 0.1 0.2; do
+  echo "== density $d default"; python tools/prof_case.py sddmm $d 5 | tail -1
+  for p in 48 40; do
+    echo "-- p=$p auto bn"; TSP_SDDMM_P=$p python tools/prof_case.py sddmm $d 5 | tail -1
+    for bn in 64 96 112; do echo "-- p=$p bn=$bn"; TSP_SDDMM_P=$p TSP_SDDMM_BN=$bn python tools/prof_case.py sddmm $d 5 | tail -1; done
+  done
+done
