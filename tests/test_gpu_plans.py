@@ -254,3 +254,34 @@ def test_spmm_non_finite_operand_reaches_only_the_rows_that_own_the_column(ops, 
     scale = oracle.spmm_abs(m, k, a.values, a.row_offsets, a.column_indices, b_fin)
     good = ~bad
     assert_close_fwd(out[good], ref[good], scale[good], what=f"spmm variant {variant}, finite part")
+
+
+def test_planned_ops_inside_a_cuda_graph(ops, dev):
+    """(a) a topology planned just before the capture, its verdict not yet on the host: no event is queried
+    under capture, the call takes the device-guarded path; (b) a topology first seen DURING the capture: no
+    plan is created (cudaMalloc is illegal there), the unplanned entry runs.  Replays give the eager result."""
+    m, k, n = 1024, 1024, 256
+    a, b = spmm_case(m, k, n, 0.3, seed=21)
+    a2, b2 = spmm_case(m, k, n, 0.08, seed=22)
+    v, ri, ro, ci = to_dev(a, dev)
+    v2, ri2, ro2, ci2 = to_dev(a2, dev)
+    bd, bd2 = _t(b, dev), _t(b2, dev)
+    lhs, rhs = _t(dense_operand((m, 512), 23, "pm1"), dev), _t(dense_operand((k, 512), 24, "pm1"), dev)
+    ops.plan_policy(0)
+    want = (ops.spmm(m, k, v, ri, ro, ci, bd), ops.sddmm(m, k, ri, ro, ci, lhs, rhs),
+            ops.spmm(m, k, v2, ri2, ro2, ci2, bd2))
+    ops.plan_policy(1)
+    side = torch.cuda.Stream(dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        ops.spmm(m, k, v, ri, ro, ci, bd)            # plans topology 1; no synchronize before the capture
+    torch.cuda.current_stream(dev).wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        got = (ops.spmm(m, k, v, ri, ro, ci, bd), ops.sddmm(m, k, ri, ro, ci, lhs, rhs),
+               ops.spmm(m, k, v2, ri2, ro2, ci2, bd2))          # topology 2 is first seen here
+    for _ in range(2):
+        graph.replay()
+    torch.cuda.synchronize()
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)

@@ -1,9 +1,4 @@
 #!/bin/bash
 set -u
-for d in 0.05 0.1 0.2; do
-  echo "== density $d default"; python tools/prof_case.py sddmm $d 5 | tail -1
-  for p in 48 40; do
-    echo "-- p=$p auto bn"; TSP_SDDMM_P=$p python tools/prof_case.py sddmm $d 5 | tail -1
-    for bn in 64 96 112; do echo "-- p=$p bn=$bn"; TSP_SDDMM_P=$p TSP_SDDMM_BN=$bn python tools/prof_case.py sddmm $d 5 | tail -1; done
-  done
-done
+timeout 900 python -m pytest tests/test_gpu_plans.py tests/test_gpu_modules.py tests/test_gpu_ref_callers.py -q 2>&1 | tail -5
+timeout 300 python tools/train_dp_transformer.py --graph 1 --steps 5 2>&1 | tail -1 | cut -c1-200

@@ -83,10 +83,22 @@ inline int plan_init_persistent(tsp_plan* p, cudaStream_t stream) {
   return 0;
 }
 
-// 1 sorted / 0 unsorted / -1 not known on the host (yet).
-inline int plan_sorted_state(tsp_plan* p) {
+inline bool stream_is_capturing(cudaStream_t stream) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
+
+// 1 sorted / 0 unsorted / -1 not known on the host (yet).  `stream`: the stream of the call that asks;
+// while it is being captured into a CUDA graph the event is NOT queried (cudaEventQuery is one of the
+// calls that invalidate a capture) -- the verdict then simply stays unknown for this call.
+inline int plan_sorted_state(tsp_plan* p, cudaStream_t stream = nullptr, bool have_stream = false) {
   int s = p->sorted.load(std::memory_order_acquire);
   if (s >= 0 || p->ephemeral || p->ev_flag == nullptr) return s;
+  if (have_stream && stream_is_capturing(stream)) return -1;
   if (cudaEventQuery(p->ev_flag) != cudaSuccess) {
     (void)cudaGetLastError();   // cudaErrorNotReady is not sticky, but keep the error state clean
     return -1;
@@ -105,7 +117,7 @@ enum { kGuardSorted = 0, kGuardUnknown = 1, kGuardUnsorted = 2 };
 inline int plan_guard(tsp_plan* p, cudaStream_t stream, StagedGuard* g, int* rc) {
   *rc = 0;
   g->flag = nullptr;
-  const int s = plan_sorted_state(p);
+  const int s = plan_sorted_state(p, stream, true);
   if (s == 1) return kGuardSorted;
   if (s == 0) return kGuardUnsorted;
   if (p->ephemeral) {
@@ -119,7 +131,10 @@ inline int plan_guard(tsp_plan* p, cudaStream_t stream, StagedGuard* g, int* rc)
       p->check_pending = true;
     }
   } else if (stream != p->flag_stream) {
-    cudaStreamWaitEvent(stream, p->ev_flag, 0);   // the check ran on another stream
+    // The check ran on another stream.  A stream under capture must not wait on an event recorded
+    // outside the capture (it would invalidate the graph): take the kernels that need no verdict.
+    if (stream_is_capturing(stream)) return kGuardUnsorted;
+    cudaStreamWaitEvent(stream, p->ev_flag, 0);
   }
   g->flag = p->d_flag;
   return kGuardUnknown;
@@ -135,15 +150,6 @@ inline int plan_flush_check(tsp_plan* p, cudaStream_t stream) {
   return 0;
 }
 
-inline bool stream_is_capturing(cudaStream_t stream) {
-  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) {
-    (void)cudaGetLastError();
-    return false;
-  }
-  return st != cudaStreamCaptureStatusNone;
-}
-
 // The view `key` of the plan's topology, built on first use.  Returns null with *rc == 0 when the
 // view cannot be built right now (a persistent plan asked for a new view while its stream is being
 // captured into a CUDA graph: cudaMalloc is illegal there) -- the caller then uses a kernel that
@@ -156,6 +162,8 @@ inline const void* plan_view(tsp_plan* p, int key, cudaStream_t stream, int* rc)
     if (!v.settled) {
       if (v.stream == stream) {
         // same stream: ordered by construction
+      } else if (stream_is_capturing(stream)) {
+        return nullptr;   // neither an event query nor a wait on an outside event is legal under capture
       } else if (cudaEventQuery(v.ev) == cudaSuccess) {
         v.settled = true;
       } else {

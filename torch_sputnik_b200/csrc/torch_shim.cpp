@@ -118,6 +118,7 @@ struct PlanEntry {
   // transposed topology, filled on demand: views of the plan's own device arrays
   torch::Tensor ro_t, ci_t, perm, ri_t;
   int64_t nnz = 0;
+  bool verdict_known = false;
   uint64_t tick = 0;
 };
 
@@ -162,6 +163,12 @@ std::shared_ptr<PlanEntry> get_plan(int64_t m, int64_t n, int64_t nnz, const tor
         e.column_indices.data_ptr() == column_indices.data_ptr()) {
       e.tick = ++c.tick;
       ++c.hits;
+      // Under CUDA-graph capture only a plan whose verdict already reached the host is used (finding it out
+      // would take an event query, which invalidates a capture); other calls take the unplanned entries.
+      if (!e.verdict_known) {
+        if (current_stream_capturing()) return nullptr;
+        e.verdict_known = tsp_plan_sorted(e.plan) >= 0;
+      }
       return it->second;
     }
     c.entries.erase(it);   // edited in place (or another view of the storage): plan again

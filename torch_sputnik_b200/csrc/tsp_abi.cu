@@ -160,7 +160,10 @@ int tsp_plan_transpose(tsp_plan* plan, void* stream_, tsp_plan** transposed_out,
     if (rc != TSP_OK) return rc;
   }
   if (!plan->t_settled && stream != plan->t_stream) {
-    if (cudaEventQuery(plan->ev_t) == cudaSuccess) {
+    if (stream_is_capturing(stream)) {
+      return invalid("tsp_plan_transpose: the transposed topology was built on another stream and is not known to be "
+                     "complete; synchronise once before capturing a CUDA graph");
+    } else if (cudaEventQuery(plan->ev_t) == cudaSuccess) {
       plan->t_settled = true;
     } else {
       (void)cudaGetLastError();
