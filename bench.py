@@ -363,6 +363,7 @@ def run_ours(args):
     barrier()
     e2e_ms = es.elapsed_time(ee) / e2e_steps
 
+    cases_f16 = half_storage_cases(torch, ops, dev, cases) if rank == 0 else None
     host_ceiling = host_copy_ceiling(torch, dist, dev, world, barrier)
     scale = scale_cases(args, torch, dist, ops, dev, world, rank, cases, barrier)
 
@@ -418,6 +419,7 @@ def run_ours(args):
                                  "bandwidth and fp32 issue, not HBM (DESIGN.md); fp32_frac is vs "
                                  f"{fp32_peak:.1f} TFLOP/s non-tensor peak"},
             "cases": table,
+            "cases_f16": cases_f16,
             "scale_cases": scale,
         }
         if not args.no_cpu_baseline:
@@ -431,6 +433,38 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def half_storage_cases(torch, ops, dev, cases):
+    """The same eight C2 operator calls with fp16 STORAGE (values, dense operands and results in
+    torch.float16; every product and sum fp32 -- the tsp_*_f16 entry points).  Reported
+    beside the fp32 `cases`, outside the headline: ms per call and useful GFLOP/s."""
+    out = []
+    try:
+        for c in cases:
+            d = c["devt"]
+            nnz = c["csr"].nnz
+            v16, dense16 = d["values"].half(), d["dense"].half()
+            lhs16, rhs16 = d["lhs"].half(), d["rhs"].half()
+            fns = (("spmm", lambda: ops.spmm(DIM, DIM, v16, d["row_indices"], d["row_offsets"], d["column_indices"], dense16)),
+                   ("sddmm", lambda: ops.sddmm(DIM, DIM, d["row_indices"], d["row_offsets"], d["column_indices"], lhs16, rhs16)))
+            for op, fn in fns:
+                for _ in range(2):
+                    fn()
+                torch.cuda.synchronize()
+                s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s.record()
+                for _ in range(5):
+                    fn()
+                e.record()
+                torch.cuda.synchronize()
+                ms = s.elapsed_time(e) / 5
+                out.append({"op": op, "density": c["density"], "ms": round(ms, 4),
+                            "useful_gflops": round(2.0 * nnz * DIM / (ms * 1e-3) / 1e9, 1)})
+            del v16, dense16, lhs16, rhs16
+        return out
+    except Exception as exc:   # measurement aid only
+        return {"unavailable": repr(exc)}
 
 
 def host_copy_ceiling(torch, dist, dev, world, barrier):

@@ -4,9 +4,12 @@
 // sparse_softmax.cu.cc:24-69): per row, y = exp(x - max) * (1 / sum(exp(x - max))) with expf
 // and one reciprocal.  The reference makes three passes over the row from global memory and
 // launches once per replica (src/softmax_cuda.cu:35-43); here one warp keeps a row of up to
-// 32*REG values in registers so every value is read once and written once, replicas ride on
-// grid.y, and the caller-side 1/sqrt(d) (modules/sparse_attention.py:72) can be folded in as
-// `scale`.  Rows longer than 32*REG fall back to the three-pass loop (L1/L2 catches re-reads).
+// 32*REG values in registers so every value is read once and written once -- as aligned 16-byte
+// vectors (4 fp32 / 8 fp16 or bf16 values per lane-load) -- replicas ride on grid.y, and the
+// caller-side 1/sqrt(d) (modules/sparse_attention.py:72) can be folded in as `scale`.  Rows longer
+// than 32*REG fall back to the three-pass loop (L1/L2 catches re-reads).
+// Summation order: lane l holds values 4l .. 4l+3 (+128 per vector) instead of l, l+32, ...; the
+// lane sums then go through the same 1,2,4,8,16 butterfly as the reference's (sparse_softmax.cu.cc:46-59).
 #pragma once
 #include "common.cuh"
 
@@ -36,22 +39,90 @@ __device__ __forceinline__ void st_once(T* p, float v) {
   else *p = Elem<T>::from_f(v);
 }
 
+constexpr int kSoftmaxRowsPerWarp = 4;
+
 template <int REG, int WARPS, typename T = float>
 __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxArgsT<T> a) {
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int item = blockIdx.x * WARPS + warp;
-  if (item >= a.m) return;
-  const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
+  // Rows are taken in storage order, not through the row swizzle: every row costs the same 8 bytes per
+  // value whatever its length, consecutive rows are consecutive in memory (the warps of a CTA stream one
+  // contiguous region), and one dependent load (row_indices -> row_offsets -> values) less heads each row.
+  // A warp takes kSoftmaxRowsPerWarp consecutive rows, one after another: with one row per warp a CTA lived
+  // for ~7000 cycles and the kernel was bound by CTA turnover (65536 CTAs at the attention shape), not by HBM.
+  for (int rr = 0; rr < kSoftmaxRowsPerWarp; ++rr) {
+  const int row = (blockIdx.x * WARPS + warp) * kSoftmaxRowsPerWarp + rr;
+  if (row >= a.m) return;
   const int beg = __ldg(a.row_offsets + row);
   const int len = __ldg(a.row_offsets + row + 1) - beg;
-  if (len <= 0) return;
+  if (len <= 0) continue;
   const size_t base = (size_t)blockIdx.y * a.nnz + beg;
   const T* __restrict__ in = a.x + base;
   T* __restrict__ out = a.out + base;
   const float scale = a.scale;
 
-  if (len <= 32 * REG) {
+  // Vector path: the row is read and written as ALIGNED 16-byte vectors (4 fp32 / 8 16-bit values per lane
+  // and load), starting at the 16-byte boundary at or before its first value; the up to V - 1 foreign
+  // values in the first and last vector are masked on the way in and never written (their vectors are
+  // stored element-wise).  A 16-byte-aligned vector that starts inside an allocation ends inside it.
+  constexpr int V = 16 / (int)sizeof(T), NV = REG / V;
+  const int mis = (int)((reinterpret_cast<uintptr_t>(in) & 15u) / sizeof(T));
+  if (NV > 0 && len + mis <= 32 * REG) {
+    const int vlen = len + mis;
+    const T* const vin = in - mis;
+    T* const vout = out - mis;
+    float v[NV > 0 ? NV : 1][V];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int e0 = (lane + 32 * j) * V;
+#pragma unroll
+      for (int t = 0; t < V; ++t) v[j][t] = -INFINITY;
+      if (e0 < vlen) {
+        unpack_raw<T, V>(v[j], ld_stream_u4(vin + e0));
+#pragma unroll
+        for (int t = 0; t < V; ++t) {
+          v[j][t] = (e0 + t >= mis && e0 + t < vlen) ? v[j][t] * scale : -INFINITY;
+          mx = fmaxf(mx, v[j][t]);
+        }
+      }
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      if (32 * j * V < vlen) {   // warp-uniform
+#pragma unroll
+        for (int t = 0; t < V; ++t) {
+          v[j][t] = expf(v[j][t] - mx);   // expf(-inf) == 0 for masked slots
+          sum += v[j][t];
+        }
+      }
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int e0 = (lane + 32 * j) * V;
+      if (e0 < vlen) {
+#pragma unroll
+        for (int t = 0; t < V; ++t) v[j][t] *= inv;
+        if (e0 >= mis && e0 + V <= vlen) {
+          if constexpr (sizeof(T) == 4) {
+            st_stream_u4(vout + e0, make_uint4(__float_as_uint(v[j][0]), __float_as_uint(v[j][1]),
+                                               __float_as_uint(v[j][2]), __float_as_uint(v[j][3])));
+          } else {
+            st_stream_u4(vout + e0, make_uint4(pack_pair<T>(v[j][0], v[j][1]), pack_pair<T>(v[j][2], v[j][3]),
+                                               pack_pair<T>(v[j][4], v[j][5]), pack_pair<T>(v[j][6], v[j][7])));
+          }
+        } else {
+#pragma unroll
+          for (int t = 0; t < V; ++t)
+            if (e0 + t >= mis && e0 + t < vlen) st_once(vout + e0 + t, v[j][t]);
+        }
+      }
+    }
+  } else if (len <= 32 * REG) {
     float v[REG];
     float mx = -INFINITY;
 #pragma unroll
@@ -87,6 +158,7 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
     for (int idx = lane; idx < len; idx += 32)
       out[idx] = Elem<T>::from_f(expf(Elem<T>::to_f(in[idx]) * scale - mx) * inv);
   }
+  }   // rows of this warp
 }
 
 // dx = scale * y * (dy - sum(dy * y)) per row.

@@ -491,7 +491,7 @@ static int pick_softmax_reg(int m, int nnz) {
   // Registers per lane so that (nearly) every row fits: mean row length + 4.5 sigma of a binomial
   // row population; longer rows take the three-pass path of the same kernel.
   const double avg = m > 0 ? (double)nnz / m : 0.0;
-  const double want = avg + 4.5 * sqrt(avg) + 1.0;
+  const double want = avg + 4.5 * sqrt(avg) + 1.0 + 7.0;   // + up to 7 slots of vector alignment slack
   if (want <= 32 * 4) return 4;
   if (want <= 32 * 8) return 8;
   if (want <= 32 * 16) return 16;
@@ -514,8 +514,10 @@ static int softmax_any(const char* name, int m, int nnz, int replicas, float sca
   a.row_offsets = row_offsets;
   a.x = static_cast<const T*>(values); a.dy = nullptr; a.out = static_cast<T*>(out);
   constexpr int WARPS = 8;
-  dim3 grid(ceil_div(m, WARPS), replicas);
-  switch (pick_softmax_reg(m, nnz)) {
+  dim3 grid(ceil_div(m, WARPS * kSoftmaxRowsPerWarp), replicas);
+  int reg = pick_softmax_reg(m, nnz);
+  if (sizeof(T) == 2 && reg < 8) reg = 8;   // one 16-byte vector = 8 values per lane
+  switch (reg) {
     case 4: csr_softmax_kernel<4, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
     case 8: csr_softmax_kernel<8, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
     case 16: csr_softmax_kernel<16, WARPS, T><<<grid, WARPS * 32, 0, stream>>>(a); break;
