@@ -181,6 +181,29 @@ int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int
                            float* values_t, void* stream);
 
 /*
+ * Many masks in ONE launch (the torch_sputnik.*_many_mask ops that tests/test_attention_many_masks.py:120-150
+ * and tests/transformer/functions.py:20-135 of the reference call and src/sputnik.cpp never binds).
+ *   b CSR masks of one shape m x n, `heads` replicas per mask: replica r (0 <= r < b*heads) uses mask r / heads.
+ *   row_offsets[b, m+1] with LOCAL offsets per mask, row_indices[b, m] (or NULL), column_indices concatenated,
+ *   nnz_prefix[b+1] a DEVICE array with the exclusive prefix of the masks' nonzero counts, max_nnz the largest count.
+ *   Dense operands are regular [b*heads, rows, cols]; values / sampled outputs are RAGGED by replica: replica r's
+ *   nnz(r/heads) values start at heads * nnz_prefix[r/heads] + (r % heads) * nnz(r/heads).
+ *   tsp_permute_values_many_f32: perm is the concatenation of the masks' permutations (indices local to a mask).
+ *   One launch of the L1-gather kernels per call, whatever b is (the reference's host loop per replica,
+ *   src/spmm_cuda.cu:48-57, would be a loop per replica AND mask).
+ */
+int tsp_sddmm_many_f32(int b, int heads, int m, int k, int n, int max_nnz, const int* nnz_prefix,
+                       const int* row_offsets, const int* column_indices, const float* lhs,
+                       const float* rhs, float* out, void* stream);
+int tsp_spmm_many_f32(int b, int heads, int m, int k, int n, int max_nnz, const int* nnz_prefix,
+                      const int* row_indices, const float* values, const int* row_offsets,
+                      const int* column_indices, const float* dense, float* out, void* stream);
+int tsp_csr_softmax_many_f32(int b, int heads, int m, int max_nnz, const int* nnz_prefix, float scale,
+                             const float* values, const int* row_offsets, float* out, void* stream);
+int tsp_permute_values_many_f32(int b, int heads, int max_nnz, const int* nnz_prefix,
+                                const float* values, const int* perm, float* values_t, void* stream);
+
+/*
  * 16-bit storage, fp32 arithmetic.  Replaces
  * sputnik::CudaSpmm / CudaSpmmBiasRelu (half2 values, short2 indices, half2 dense; float bias)
  * third_party/sputnik/sputnik/spmm/cuda_spmm.cu.cc:511-570, contract cuda_spmm.h:75-127 -- which the

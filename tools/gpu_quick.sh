@@ -1,8 +1,4 @@
 #!/bin/bash
 set -u
-mkdir -p gpurun_out
-for dt in f16 f32; do
-TSP_DTYPE=$dt timeout 300 ncu --set full --clock-control none --profile-from-start off -c 1 -f -o gpurun_out/r02_softmax_$dt python tools/prof_c4.py softmax 128 2 > /dev/null 2>&1
-python tools/ncu_summary.py gpurun_out/r02_softmax_$dt.ncu-rep | grep -E "==|time_duration|dram__bytes|dram__thr|warps_active|lsu_wavefronts.avg|issue_active|inst_executed.sum|scoreboard|lg_throttle|occupancy_limit|registers|lts__t_sector_hit|mio_thr"
-done
-rm -f gpurun_out/r02_softmax_*.ncu-rep
+for n in 512 1024 4096; do python tools/prof_case.py spmm 0.25 4 $n | tail -1; done
+timeout 900 python -m pytest tests/test_gpu_many_mask.py tests/test_gpu_ref_callers.py tests/test_gpu_spmm.py tests/test_gpu_modules.py tests/test_gpu_sharding.py -q 2>&1 | tail -4

@@ -19,6 +19,7 @@ SYMBOLS = (
     "tsp_spmm_f16", "tsp_spmm_bf16", "tsp_sddmm_f16", "tsp_sddmm_bf16", "tsp_csr_softmax_f16", "tsp_csr_softmax_bf16",
     "tsp_permute_values_b16", "tsp_plan_spmm_b16", "tsp_plan_sddmm_b16",
     "tsp_sparse_attention_supported_b16", "tsp_sparse_attention_b16",
+    "tsp_sddmm_many_f32", "tsp_spmm_many_f32", "tsp_csr_softmax_many_f32", "tsp_permute_values_many_f32",
 )
 
 _lib = None
@@ -47,6 +48,10 @@ def load() -> ctypes.CDLL:
         lib.tsp_sparse_attention_f32.argtypes = [i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_sparse_attention_supported_b16.argtypes = [i, i]
         lib.tsp_sparse_attention_b16.argtypes = [i, i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        lib.tsp_sddmm_many_f32.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp]
+        lib.tsp_spmm_many_f32.argtypes = [i, i, i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp]
+        lib.tsp_csr_softmax_many_f32.argtypes = [i, i, i, i, vp, f, vp, vp, vp, vp]
+        lib.tsp_permute_values_many_f32.argtypes = [i, i, i, vp, vp, vp, vp, vp]
         lib.tsp_set_variant.argtypes = [ctypes.c_char_p, i]
         lib.tsp_launch_count.restype = ctypes.c_ulonglong
         for name in ("tsp_spmm_f16", "tsp_spmm_bf16"):

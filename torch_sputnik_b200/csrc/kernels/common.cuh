@@ -214,6 +214,38 @@ __device__ __forceinline__ void raster_tile(int t, int rows, int cols, int srb, 
   c = g * scb + (tg - rl * w);
 }
 
+// ---- many masks in one launch (the *_many_mask ops: tests/test_attention_many_masks.py:120-150,
+// tests/transformer/functions.py of the reference) -------------------------------------------------
+// b CSR masks of one shape share a launch: replica r uses mask r / heads.  Mask i's topology is
+// row_offsets + i * (m + 1) (LOCAL offsets), column_indices + prefix[i], row_indices + i * m;
+// values / sampled outputs are ragged by replica: replica r's nnz_i values start at
+// heads * prefix[i] + (r % heads) * nnz_i.  prefix == null: one shared topology (the usual case).
+struct MaskTable {
+  const int* prefix = nullptr;   // device int[b + 1]: exclusive prefix of the masks' nonzero counts
+  int heads = 1;
+};
+struct MaskView {
+  long long topo_rows;    // offset into row_offsets / row_indices, in rows (mask * (m + 1) resp. mask * m)
+  long long cols;         // offset into column_indices
+  long long values;       // offset of this replica's values / sampled outputs
+  int nnz;                // nonzeros of this replica's mask
+  int mask;
+};
+__device__ __forceinline__ MaskView mask_view(const MaskTable& t, int rep, int nnz_shared) {
+  MaskView v;
+  if (t.prefix == nullptr) {
+    v.mask = 0; v.topo_rows = 0; v.cols = 0; v.nnz = nnz_shared; v.values = (long long)rep * nnz_shared;
+  } else {
+    v.mask = rep / t.heads;
+    const int p0 = __ldg(t.prefix + v.mask);
+    v.nnz = __ldg(t.prefix + v.mask + 1) - p0;
+    v.cols = p0;
+    v.values = (long long)t.heads * p0 + (long long)(rep - v.mask * t.heads) * v.nnz;
+    v.topo_rows = v.mask;   // scaled by (m + 1) or m at the point of use
+  }
+  return v;
+}
+
 // ---- storage types: fp32, or fp16 / bf16 storage with fp32 arithmetic (the
 // reference's half SpMM, cuda_spmm.cu.cc:511-570, keeps fp32 accumulators the same way) -------------
 template <typename T>

@@ -25,6 +25,7 @@ struct SoftmaxArgsT {
   const T* x;   // forward: values; backward: y
   const T* dy;  // backward only
   T* out;
+  MaskTable masks;   // many masks in one launch (forward kernel)
 };
 using SoftmaxArgs = SoftmaxArgsT<float>;
 
@@ -53,10 +54,12 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
   for (int rr = 0; rr < kSoftmaxRowsPerWarp; ++rr) {
   const int row = (blockIdx.x * WARPS + warp) * kSoftmaxRowsPerWarp + rr;
   if (row >= a.m) return;
-  const int beg = __ldg(a.row_offsets + row);
-  const int len = __ldg(a.row_offsets + row + 1) - beg;
+  const MaskView mv = mask_view(a.masks, blockIdx.y, a.nnz);
+  const int* __restrict__ row_offsets = a.row_offsets + mv.topo_rows * (a.m + 1);
+  const int beg = __ldg(row_offsets + row);
+  const int len = __ldg(row_offsets + row + 1) - beg;
   if (len <= 0) continue;
-  const size_t base = (size_t)blockIdx.y * a.nnz + beg;
+  const size_t base = (size_t)mv.values + beg;
   const T* __restrict__ in = a.x + base;
   T* __restrict__ out = a.out + base;
   const float scale = a.scale;

@@ -187,14 +187,17 @@ __global__ void __launch_bounds__(256) transpose_finish_kernel(const TransposeFi
 }
 
 // V: float, or unsigned short for any 16-bit storage type (a pure move).
+// masks.prefix != null: many masks in one launch -- replica blockIdx.y uses perm + prefix[mask] (indices LOCAL
+// to the mask) and the ragged value layout of MaskTable; nnz is then the largest mask's count.
 template <typename V>
 __global__ void __launch_bounds__(256)
 permute_values_kernel(int nnz, const V* __restrict__ values, const int* __restrict__ perm,
-                      V* __restrict__ values_t) {
+                      V* __restrict__ values_t, const MaskTable masks) {
   const int p = blockIdx.x * 256 + threadIdx.x;
-  if (p >= nnz) return;
-  const size_t base = (size_t)blockIdx.y * nnz;
-  values_t[base + p] = __ldg(values + base + __ldg(perm + p));
+  const MaskView mv = mask_view(masks, blockIdx.y, nnz);
+  if (p >= mv.nnz) return;
+  const size_t base = (size_t)mv.values;
+  values_t[base + p] = __ldg(values + base + __ldg(perm + mv.cols + p));
 }
 
 __global__ void fill_int_kernel(int* __restrict__ dst, int count, int value) {

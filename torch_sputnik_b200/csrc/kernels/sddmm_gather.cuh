@@ -33,6 +33,7 @@ struct SddmmArgsT {
   // weight gradient of a sparse linear layer); the staged kernels fold the replica loop into
   // their k loop, grid.y is 1.
   int reduce_reps = 0;
+  MaskTable masks;   // many masks in one launch (rows / gather kernels only); a.nnz is then the LARGEST mask's count
 };
 using SddmmArgs = SddmmArgsT<float>;
 
@@ -73,8 +74,12 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   const int lane = threadIdx.x & 31;
   const int chunk = blockIdx.x * WARPS + warp;
   const int j0 = chunk * 32;
-  if (j0 >= a.nnz) return;
   const int rep = blockIdx.y;
+  const MaskView mv = mask_view(a.masks, rep, a.nnz);
+  const int nnz = mv.nnz;
+  if (j0 >= nnz) return;
+  const int* __restrict__ row_offsets = a.row_offsets + mv.topo_rows * (a.m + 1);
+  const int* __restrict__ column_indices = a.column_indices + mv.cols;
   const int k = a.k;
   // reduce_reps > 0: one output vector, the replica loop runs here (grid.y == 1)
   const int nrep = a.reduce_reps > 0 ? a.reduce_reps : 1;
@@ -86,9 +91,9 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
   int my_row = 0, my_col = 0;
   {
     const int j = j0 + lane;
-    if (j < a.nnz) {
-      my_row = row_of_nonzero(a.row_offsets, a.m, j);
-      my_col = __ldg(a.column_indices + j);
+    if (j < nnz) {
+      my_row = row_of_nonzero(row_offsets, a.m, j);
+      my_col = __ldg(column_indices + j);
     }
   }
 
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
       const int src = grp * NPG + i;
       const int r = __shfl_sync(kFullMask, my_row, src);
       const int c = __shfl_sync(kFullMask, my_col, src);
-      if (kin && (j0 + src) < a.nnz) {
+      if (kin && (j0 + src) < nnz) {
         if (r != prev_row) {
           load_elems<T, VEC>(av, lhs + (size_t)r * k + kofs);
           prev_row = r;
@@ -126,7 +131,7 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_gather_kernel(const SddmmArg
 
   transpose_reduce<LPN>(acc, lane);
   const int j = j0 + grp * NPG + sub;
-  if (j < a.nnz) a.out[(size_t)rep * a.nnz + j] = Elem<T>::from_f(acc[0]);
+  if (j < nnz) a.out[mv.values + j] = Elem<T>::from_f(acc[0]);
 }
 
 // out[j] = sum_r scratch[r, j] (ascending r).

@@ -43,10 +43,12 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT
   const int rep = blockIdx.y;
   const int q = lane >> 3, sub = lane & 7;
 
-  const int beg = __ldg(a.row_offsets + row), end = __ldg(a.row_offsets + row + 1);
+  const MaskView mv = mask_view(a.masks, rep, a.nnz);
+  const int* __restrict__ row_offsets = a.row_offsets + mv.topo_rows * (a.m + 1);
+  const int beg = __ldg(row_offsets + row), end = __ldg(row_offsets + row + 1);
   if (beg >= end) return;
-  const int* __restrict__ cols = a.column_indices;
-  T* __restrict__ out = a.out + (size_t)rep * a.nnz;
+  const int* __restrict__ cols = a.column_indices + mv.cols;
+  T* __restrict__ out = a.out + mv.values;
   // this lane's chunk `sub` of rhs row 0 (16-byte units); chunk cc of row c is at + c * (8 * KC) + cc * 8
   const T* const rbase = a.rhs + (size_t)rep * a.n * K + sub * E;
   const T* const lrow = a.lhs + ((size_t)rep * a.m + row) * K + sub * E;

@@ -37,6 +37,7 @@ struct SpmmArgsT {
   // guard_flag != null: this launch is the unsorted-columns fallback of a staged launch and runs
   // only if the sorted-columns check raised *guard_flag (a device word owned by the call's plan).
   const unsigned* guard_flag = nullptr;
+  MaskTable masks;   // many masks in one launch (gather kernel only)
 };
 using SpmmArgs = SpmmArgsT<float>;
 
@@ -106,8 +107,9 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
   const int lane = threadIdx.x & 31;
   const int item = blockIdx.x * WARPS + warp;
   if (item >= a.m) return;
-  const int row = a.row_indices ? __ldg(a.row_indices + item) : item;
   const int rep = blockIdx.z;
+  const MaskView mv = mask_view(a.masks, rep, a.nnz);
+  const int row = a.row_indices ? __ldg(a.row_indices + mv.topo_rows * a.m + item) : item;
 
   const int n = a.n;
   const int n0 = blockIdx.y * (32 * VEC * U) + lane * VEC;
@@ -117,8 +119,8 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
 #pragma unroll
   for (int u = 0; u < U; ++u) lane_base[u] = reinterpret_cast<const V*>(dense + n0 + u * 32 * VEC);
   const unsigned row_vecs = (unsigned)n / VEC;
-  const float* __restrict__ vals = a.values + (size_t)rep * a.values_stride;
-  const int* __restrict__ cols = a.column_indices;
+  const float* __restrict__ vals = a.masks.prefix ? a.values + mv.values : a.values + (size_t)rep * a.values_stride;
+  const int* __restrict__ cols = a.column_indices + mv.cols;
 
   bool ok[U];
 #pragma unroll
@@ -130,8 +132,9 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_gather_kernel(const SpmmArgs 
 #pragma unroll
     for (int v = 0; v < VEC; ++v) acc[u][v] = 0.f;
 
-  const int beg = __ldg(a.row_offsets + row);
-  const int end = __ldg(a.row_offsets + row + 1);
+  const int* __restrict__ row_offsets = a.row_offsets + mv.topo_rows * (a.m + 1);
+  const int beg = __ldg(row_offsets + row);
+  const int end = __ldg(row_offsets + row + 1);
 
   int2* sp = s_pairs[warp];
   for (int base = beg; base < end; base += 32) {

@@ -444,7 +444,11 @@ inline int launch_spmm_staged(const SpmmArgs& a, int replicas, cudaStream_t stre
   } else {
     int U = (int)ceil(want / 8.0);
     U = U < 1 ? 1 : (U > 4 ? 4 : U);
-    if (a.n > 128) {
+    // 256-column tiles (2 CTAs per SM) unless they leave the machine half empty: a column-sharded SpMM
+    // (n = 512 per rank at 8 GPUs) has 74 x 2 = 148 such tiles for 296 CTA slots; 128-column tiles double
+    // the CTA count at the same bytes per FMA.
+    const long long wide_ctas = (long long)ceil_div(a.m, 56) * ceil_div(a.n, 256) * replicas;
+    if (a.n > 128 && wide_ctas >= 2LL * sm_count()) {
       switch (U) {
         case 1: rc = launch_spmm_staged_cfg<StagedCfg<2, 4, 2, 3, 7, 1>>(a, replicas, guard, stream); break;
         case 2: rc = launch_spmm_staged_cfg<StagedCfg<2, 4, 2, 3, 7, 2>>(a, replicas, guard, stream); break;

@@ -218,6 +218,20 @@ static int try_spmm_band(tsp_plan* plan, SpmmArgsT<T>& a, int replicas, cudaStre
 extern "C" {
 
 // ------------------------------------------------------------------------------------ SpMM
+// The gather kernel with the widest vector the operand layout allows.
+static void launch_spmm_gather_any(const SpmmArgs& a, int replicas, cudaStream_t stream) {
+  const int n = a.n;
+  const bool vec4_ok = (n % 4 == 0) && aligned16(a.dense) && aligned16(a.out);
+  const bool vec2_ok = (n % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.dense) & 7u) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(a.out) & 7u) == 0);
+  if (vec4_ok && n > 128) launch_spmm_gather<4, 2>(a, replicas, stream);
+  else if (vec4_ok && n > 64) launch_spmm_gather<4, 1>(a, replicas, stream);
+  else if (vec2_ok && n > 64) launch_spmm_gather<2, 2>(a, replicas, stream);
+  else if (vec2_ok && n > 32) launch_spmm_gather<2, 1>(a, replicas, stream);
+  else if (n > 32) launch_spmm_gather<1, 2>(a, replicas, stream);
+  else launch_spmm_gather<1, 1>(a, replicas, stream);
+}
+
 static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, const int* row_indices,
                      const float* values, const int* value_perm_or_null, const float* dense,
                      const float* bias_or_null, int relu, float* out, cudaStream_t stream) {
@@ -252,8 +266,6 @@ static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, con
     // st == 1: the gather launch below is the guarded fallback; st == -1: it is the kernel
   }
   const bool vec4_ok = (n % 4 == 0) && aligned16(dense) && aligned16(out);
-  const bool vec2_ok = (n % 2 == 0) && ((reinterpret_cast<uintptr_t>(dense) & 7u) == 0) &&
-                       ((reinterpret_cast<uintptr_t>(out) & 7u) == 0);
 
   // variant: 0 = heuristic, 1 = gather, 2 = staged (rows per group from density), 3 = staged with
   // 4-row groups, 4 = staged with 8-row groups.
@@ -287,19 +299,7 @@ static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, con
     TSP_CHECK_LAUNCH("tsp_spmm_f32 (rowsplit)");
     return TSP_OK;
   }
-  if (vec4_ok && n > 128) {
-    launch_spmm_gather<4, 2>(a, replicas, stream);
-  } else if (vec4_ok && n > 64) {
-    launch_spmm_gather<4, 1>(a, replicas, stream);
-  } else if (vec2_ok && n > 64) {
-    launch_spmm_gather<2, 2>(a, replicas, stream);
-  } else if (vec2_ok && n > 32) {
-    launch_spmm_gather<2, 1>(a, replicas, stream);
-  } else if (n > 32) {
-    launch_spmm_gather<1, 2>(a, replicas, stream);
-  } else {
-    launch_spmm_gather<1, 1>(a, replicas, stream);
-  }
+  launch_spmm_gather_any(a, replicas, stream);
   TSP_CHECK_LAUNCH("tsp_spmm_f32 (gather)");
   return TSP_OK;
 }
@@ -700,7 +700,7 @@ int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int
   if (nnz == 0 || replicas == 0) return TSP_OK;
   if (!values || !perm || !values_t) return invalid("tsp_permute_values_f32: null pointer argument");
   dim3 grid(ceil_div(nnz, 256), replicas);
-  permute_values_kernel<float><<<grid, 256, 0, stream>>>(nnz, values, perm, values_t);
+  permute_values_kernel<float><<<grid, 256, 0, stream>>>(nnz, values, perm, values_t, MaskTable{});
   TSP_CHECK_LAUNCH("tsp_permute_values_f32");
   return TSP_OK;
 }
@@ -714,8 +714,103 @@ int tsp_permute_values_b16(int nnz, int replicas, const void* values, const int*
   if (!values || !perm || !values_t) return invalid("tsp_permute_values_b16: null pointer argument");
   dim3 grid(ceil_div(nnz, 256), replicas);
   permute_values_kernel<unsigned short><<<grid, 256, 0, stream>>>(
-      nnz, static_cast<const unsigned short*>(values), perm, static_cast<unsigned short*>(values_t));
+      nnz, static_cast<const unsigned short*>(values), perm, static_cast<unsigned short*>(values_t), MaskTable{});
   TSP_CHECK_LAUNCH("tsp_permute_values_b16");
+  return TSP_OK;
+}
+
+// ----------------------------------------------------------------- many masks in one launch
+static int many_check(const char* name, int b, int heads, int m, const int* prefix, const int* row_offsets) {
+  if (b < 1 || heads < 1 || m < 0) return invalid("%s: bad mask count / heads / m (b=%d heads=%d m=%d)", name, b, heads, m);
+  if ((long long)b * heads > 65535) return invalid("%s: b * heads = %lld exceeds 65535", name, (long long)b * heads);
+  if (!prefix || !row_offsets) return invalid("%s: null pointer argument", name);
+  return TSP_OK;
+}
+
+int tsp_sddmm_many_f32(int b, int heads, int m, int k, int n, int max_nnz, const int* nnz_prefix,
+                       const int* row_offsets, const int* column_indices, const float* lhs, const float* rhs,
+                       float* out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = many_check("tsp_sddmm_many_f32", b, heads, m, nnz_prefix, row_offsets)) return rc;
+  if (k < 0 || n < 0 || max_nnz < 0) return invalid("tsp_sddmm_many_f32: negative dimension");
+  if (max_nnz == 0 || m == 0) return TSP_OK;
+  if (!column_indices || !out || (k > 0 && (!lhs || !rhs))) return invalid("tsp_sddmm_many_f32: null pointer argument");
+  SddmmArgs a;
+  a.m = m; a.k = k; a.n = n; a.nnz = max_nnz;
+  a.row_offsets = row_offsets;
+  a.column_indices = column_indices;
+  a.lhs = lhs; a.rhs = rhs; a.out = out;
+  a.masks.prefix = nnz_prefix;
+  a.masks.heads = heads;
+  if (sddmm_rows_applicable(a)) launch_sddmm_rows(a, b * heads, stream);
+  else launch_sddmm_gather_any(a, b * heads, stream);
+  TSP_CHECK_LAUNCH("tsp_sddmm_many_f32");
+  return TSP_OK;
+}
+
+int tsp_spmm_many_f32(int b, int heads, int m, int k, int n, int max_nnz, const int* nnz_prefix,
+                      const int* row_indices, const float* values, const int* row_offsets,
+                      const int* column_indices, const float* dense, float* out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = many_check("tsp_spmm_many_f32", b, heads, m, nnz_prefix, row_offsets)) return rc;
+  if (k < 0 || n < 0 || max_nnz < 0) return invalid("tsp_spmm_many_f32: negative dimension");
+  if (m == 0 || n == 0) return TSP_OK;
+  if (!out || (max_nnz > 0 && (!values || !column_indices || !dense))) return invalid("tsp_spmm_many_f32: null pointer argument");
+  SpmmArgs a;
+  a.m = m; a.k = k; a.n = n; a.nnz = max_nnz;
+  a.values_stride = 0;
+  a.row_indices = row_indices;
+  a.values = values;
+  a.row_offsets = row_offsets;
+  a.column_indices = column_indices;
+  a.dense = dense;
+  a.bias = nullptr;
+  a.relu = 0;
+  a.out = out;
+  a.masks.prefix = nnz_prefix;
+  a.masks.heads = heads;
+  launch_spmm_gather_any(a, b * heads, stream);
+  TSP_CHECK_LAUNCH("tsp_spmm_many_f32");
+  return TSP_OK;
+}
+
+int tsp_csr_softmax_many_f32(int b, int heads, int m, int max_nnz, const int* nnz_prefix, float scale,
+                             const float* values, const int* row_offsets, float* out, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (int rc = many_check("tsp_csr_softmax_many_f32", b, heads, m, nnz_prefix, row_offsets)) return rc;
+  if (max_nnz <= 0 || m == 0) return TSP_OK;
+  if (!values || !out) return invalid("tsp_csr_softmax_many_f32: null pointer argument");
+  SoftmaxArgs a;
+  a.m = m; a.nnz = max_nnz; a.scale = scale;
+  a.row_indices = nullptr;
+  a.row_offsets = row_offsets;
+  a.x = values; a.dy = nullptr; a.out = out;
+  a.masks.prefix = nnz_prefix;
+  a.masks.heads = heads;
+  constexpr int WARPS = 8;
+  dim3 grid(ceil_div(m, WARPS * kSoftmaxRowsPerWarp), b * heads);
+  switch (pick_softmax_reg(m, max_nnz)) {
+    case 4: csr_softmax_kernel<4, WARPS, float><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 8: csr_softmax_kernel<8, WARPS, float><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    case 16: csr_softmax_kernel<16, WARPS, float><<<grid, WARPS * 32, 0, stream>>>(a); break;
+    default: csr_softmax_kernel<32, WARPS, float><<<grid, WARPS * 32, 0, stream>>>(a); break;
+  }
+  TSP_CHECK_LAUNCH("tsp_csr_softmax_many_f32");
+  return TSP_OK;
+}
+
+int tsp_permute_values_many_f32(int b, int heads, int max_nnz, const int* nnz_prefix, const float* values,
+                                const int* perm, float* values_t, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (b < 1 || heads < 1 || (long long)b * heads > 65535) return invalid("tsp_permute_values_many_f32: bad b / heads");
+  if (max_nnz <= 0) return TSP_OK;
+  if (!nnz_prefix || !values || !perm || !values_t) return invalid("tsp_permute_values_many_f32: null pointer argument");
+  MaskTable t;
+  t.prefix = nnz_prefix;
+  t.heads = heads;
+  dim3 grid(ceil_div(max_nnz, 256), b * heads);
+  permute_values_kernel<float><<<grid, 256, 0, stream>>>(max_nnz, values, perm, values_t, t);
+  TSP_CHECK_LAUNCH("tsp_permute_values_many_f32");
   return TSP_OK;
 }
 
