@@ -61,12 +61,19 @@ def test_attention_chain_many_mask(b, h, m, k, dens, stacked):
     v = dense_operand((R, m, k), 3, "pm1")
     tq, tk, tv = (torch.from_numpy(x).to(dev) for x in (q, kk, v))
 
+    tsp.sddmm_many_mask(b, m, m, nnz, ri, ro, ci, tq, tk)          # (first sight: the prefix table is uploaded and cached)
+    before = tsp.launch_count()
     scores = tsp.sddmm_many_mask(b, m, m, nnz, ri, ro, ci, tq, tk)
+    assert tsp.launch_count() - before == 1                        # ONE kernel for all b masks x h heads
     uniform = len({c.column_indices.size for c in masks}) == 1
     assert scores.dim() == (2 if uniform else 1)
+    before = tsp.launch_count()
     probs = tsp.sparse_softmax_many_mask(b, m, nnz, scores, ri, ro, ci)
     out = tsp.spmm_many_mask(b, m, m, nnz, probs, ri, ro, ci, tv)
+    assert tsp.launch_count() - before == 2
     assert out.shape == (R, m, k)
+    scaled = tsp.sparse_softmax_many_mask_scaled(b, m, nnz, scores, ri, ro, ci, 0.25)
+    torch.testing.assert_close(scaled, tsp.sparse_softmax_many_mask(b, m, nnz, scores * 0.25, ri, ro, ci), rtol=1e-5, atol=1e-7)
     torch.cuda.synchronize()
 
     s_np = _split(scores.cpu().numpy().reshape(-1), masks, h)
@@ -96,6 +103,10 @@ def test_csr_transpose_many_mask(stacked):
     total = int(nnz.sum())
     vals = dense_operand((h * total,), 9, "pm1")
     vt, rot, cit = tsp.csr_transpose_many_mask(b, m, n, nnz, torch.from_numpy(vals).to(dev), ro, ci)
+    before = tsp.launch_count()
+    vt2, rot2, cit2 = tsp.csr_transpose_many_mask(b, m, n, nnz, torch.from_numpy(vals).to(dev), ro, ci)
+    assert tsp.launch_count() - before == 1                        # every mask sorted once; afterwards one gather launch
+    assert torch.equal(vt, vt2) and rot2.data_ptr() == rot.data_ptr() and cit2.data_ptr() == cit.data_ptr()
     torch.cuda.synchronize()
     assert rot.shape == (b, n + 1) and rot.dtype == torch.int32
     v_in = _split(vals, masks, h)
