@@ -192,8 +192,13 @@ inline const void* plan_view(tsp_plan* p, int key, cudaStream_t stream, int* rc)
   const int brc = key == kBitmapKey
                       ? build_sddmm_tiled_view(p->row_offsets, p->column_indices, p->m, ceil_div(p->n, 64), ws, flag, stream)
                       : build_sddmm_sampled_view(p->row_offsets, p->column_indices, p->m, p->n, key, ws, flag, stream);
+  if (brc != 0) {   // the build did not launch: do not keep a view nobody filled
+    if (p->ephemeral) cudaFreeAsync(ws, stream); else cudaFree(ws);
+    *rc = brc;
+    return nullptr;
+  }
   tsp_plan::View v{key, ws, nullptr, stream, p->ephemeral};
-  if (brc == 0 && !p->ephemeral) {
+  if (!p->ephemeral) {
     if (cudaEventCreateWithFlags(&v.ev, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventRecord(v.ev, stream) != cudaSuccess) {
       (void)cudaGetLastError();
