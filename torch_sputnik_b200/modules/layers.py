@@ -47,9 +47,14 @@ class SparseLinear(nn.Module):
         self.column_indices = column_indices
 
     def forward(self, x):
+        return self.forward_channels_first(x.transpose(1, 2).contiguous())
+
+    def forward_channels_first(self, xt):
+        """xt [B, in, tokens] (contiguous) -> [B, out, tokens]: the layout the kernel works in.  Callers that
+        chain sparse layers stay in it and skip the ``transpose().contiguous()`` round trip the reference
+        makes around every layer (modules/sparse_linear.py:89, modules/sparse_attention.py:108-126)."""
         return SparseLinearFunction.apply(self.output_features, self.input_features, self.values,
-                                          self.row_indices, self.row_offsets, self.column_indices,
-                                          x.transpose(1, 2).contiguous())
+                                          self.row_indices, self.row_offsets, self.column_indices, xt)
 
 
 class SparseAttention(nn.Module):
@@ -88,10 +93,22 @@ class SparseAttention(nn.Module):
                           self.column_indices, v3d)
 
     def forward(self, query, key, value, mask=None):
+        """Same function as the reference's forward (modules/sparse_attention.py:100-128), with the layout
+        round trips fused: a projection's output [B, E, S] IS [B, H, D, S], so one transpose of the last two
+        dimensions gives the [B*H, S, D] operand of the sparse ops (the reference copies twice: to [B, S, E]
+        and again when flattening the heads); the context goes back to [B, E, S] with one transpose and
+        feeds the output projection in its own layout; a shared input (self-attention) is transposed once."""
         batch = query.size(0)
-        # SparseLinear returns [B, E, S]; bring it to [B, H, S, D].
-        q, k, v = (lin(x).transpose(1, 2).contiguous().view(batch, -1, self.num_heads, self.head_dim)
-                   .transpose(1, 2) for lin, x in zip(self.linears, (query, key, value)))
-        ctx = self.attention(q, k, v, mask).reshape(batch, self.num_heads, -1, self.head_dim)
-        merged = ctx.transpose(1, 2).contiguous().reshape(batch, -1, self.num_heads * self.head_dim)
-        return self.linears[-1](merged).transpose(1, 2)
+        h, d = self.num_heads, self.head_dim
+        cf = {}
+
+        def channels_first(x):
+            key_ = id(x)
+            if key_ not in cf:
+                cf[key_] = x.transpose(1, 2).contiguous()            # [B, E, S]
+            return cf[key_]
+        q, k, v = (lin.forward_channels_first(channels_first(x)).view(batch, h, d, -1).transpose(2, 3)
+                   for lin, x in zip(self.linears, (query, key, value)))   # [B, H, S, D] views
+        ctx = self.attention(q, k, v, mask).reshape(batch, h, -1, d)        # [B, H, S, D]
+        merged_cf = ctx.transpose(2, 3).reshape(batch, h * d, -1)           # [B, E, S], one copy
+        return self.linears[-1].forward_channels_first(merged_cf).transpose(1, 2)

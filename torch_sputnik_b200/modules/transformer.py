@@ -31,8 +31,8 @@ class SparseMLP(nn.Module):
         self.down = SparseLinear(ffn, hidden)
 
     def forward(self, x):                                   # x [B, S, hidden]
-        h = torch.relu(self.up(x).transpose(1, 2))          # SparseLinear returns [B, out, S]
-        return self.down(h.contiguous()).transpose(1, 2)
+        h = torch.relu(self.up(x))                          # [B, ffn, S]: stays in the kernels' layout
+        return self.down.forward_channels_first(h).transpose(1, 2)
 
 
 class SparseEncoderLayer(nn.Module):
