@@ -168,8 +168,9 @@ class SparseLinearFunction(torch.autograd.Function):
                                            dense.contiguous())
         if ctx.needs_input_grad[6]:
             t = TransposedTopology.get(m, k, row_offsets, column_indices)
-            values_t = ops.permute_values(values.contiguous(), t.perm)
-            grad_dense = ops.left_spmm(k, m, values_t, t.row_indices, t.row_offsets,
+            # W^T @ dY on the plan's transposed topology, the weights read through the permutation
+            # (one launch; no permuted copy of the values)
+            grad_dense = ops.spmm_perm(k, m, values.contiguous(), t.perm, t.row_indices, t.row_offsets,
                                        t.column_indices, grad_output).reshape(dense.shape)
         return None, None, grad_values, None, None, None, grad_dense
 
