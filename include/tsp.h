@@ -212,7 +212,9 @@ int tsp_permute_values_many_f32(int b, int heads, int max_nnz, const int* nnz_pr
  * lhs / rhs / out point at IEEE fp16 (..._f16) or bfloat16 (..._bf16) elements; indices stay int32
  * (no short2 packing, so k is not limited to 32767), any nnz per row, any n (16-byte-aligned rows
  * take the 8-element vector path).  Every product and sum is fp32, each result is rounded to the
- * storage type once.  bias stays fp32.  Argument meaning otherwise as tsp_spmm_perm_f32 /
+ * storage type once.  Large dense-ish problems (where the fp32 path would stage dense tiles in shared
+ * memory) widen the operands once into stream-ordered fp32 scratch, run the fp32 kernel and round the
+ * result on the way back -- same arithmetic.  bias stays fp32.  Argument meaning otherwise as tsp_spmm_perm_f32 /
  * tsp_sddmm_f32 / tsp_csr_softmax_f32.  tsp_permute_values_b16 moves any 16-bit element type.
  */
 int tsp_spmm_f16(int m, int k, int n, int nnz, int replicas, int values_shared,

@@ -250,3 +250,29 @@ def test_mixed_dtypes_are_rejected(ops, dev):
         ops.sddmm(16, 16, ri, ro, ci, torch.zeros(16, 8, device=dev).half(), torch.zeros(16, 8, device=dev).bfloat16())
     with pytest.raises(RuntimeError, match="float32 only"):
         ops.sddmm_reduce(16, 16, ri, ro, ci, torch.zeros(2, 16, 8, device=dev).half(), torch.zeros(2, 16, 8, device=dev).half())
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("density", [0.4, 0.08])
+def test_16bit_storage_through_the_fp32_staged_kernels(ops, dev, dtype, density):
+    """Big, dense-ish shapes: the 16-bit operands are widened once, the fp32 staged kernel (merged-row SpMM, tiled /
+    sampled SDDMM) runs and the result is rounded once -- same contract, checked against the fp64 oracle; and the
+    result equals the fp32 op on the widened operands rounded to the storage type, bit for bit."""
+    m, k, n = 1024, 1024, 512
+    a = random_csr(m, k, density, seed=70, values="pm1")
+    ri, ro, ci = _t(a.row_indices, dev), _t(a.row_offsets, dev), _t(a.column_indices, dev)
+    vals, v32 = _q(a.values, dtype, dev)
+    dense, d32 = _q(dense_operand((k, n), 71, "pm1"), dtype, dev)
+    out = ops.spmm(m, k, vals, ri, ro, ci, dense)
+    assert out.dtype == dtype
+    ref = oracle.spmm(m, k, v32, a.row_offsets, a.column_indices, d32).astype(np.float64)
+    _check(out, ref, oracle.spmm_abs(m, k, v32, a.row_offsets, a.column_indices, d32), dtype, "spmm, widened")
+    if density >= 0.35:
+        assert torch.equal(out, ops.spmm(m, k, vals.float(), ri, ro, ci, dense.float()).to(dtype))
+    lhs, l32 = _q(dense_operand((m, n), 72, "pm1"), dtype, dev)
+    rhs, r32 = _q(dense_operand((k, n), 73, "pm1"), dtype, dev)
+    sc = ops.sddmm(m, k, ri, ro, ci, lhs, rhs)
+    assert sc.dtype == dtype
+    sref = oracle.sddmm(m, k, a.row_offsets, a.column_indices, l32, r32).astype(np.float64)
+    _check(sc, sref, oracle.sddmm_abs(m, k, a.row_offsets, a.column_indices, l32, r32), dtype, "sddmm, widened")
+    assert torch.equal(sc, ops.sddmm(m, k, ri, ro, ci, lhs.float(), rhs.float()).to(dtype))

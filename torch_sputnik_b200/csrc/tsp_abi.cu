@@ -818,6 +818,88 @@ int tsp_permute_values_many_f32(int b, int heads, int max_nnz, const int* nnz_pr
 // (all gather-type kernels: no topology views, so no plan is involved)
 }  // extern "C"
 
+// ---- 16-bit storage through the fp32 staged kernels -------------------------------------------------
+// Where the fp32 path would take a kernel that stages dense tiles in shared memory (SpMM at density >=
+// 0.22, SDDMM with a long inner dimension), arithmetic -- not operand bytes -- is the bound, and the
+// 16-bit gather kernels lose to it (fp16 SDDMM at 4096^3, density 0.5: 9.9 ms gathered against 2.9 ms
+// tiled in fp32).  There the 16-bit operands are widened once into stream-ordered fp32 scratch (an
+// HBM-bound pass of ~30 us per 64 MB), the fp32 kernel runs, and the result is rounded once on the way
+// back: the same contract (fp32 products and sums, one rounding of the result), never slower than the
+// fp32 call by more than the two conversion passes.
+template <typename T>
+__global__ void __launch_bounds__(256) widen_kernel(const T* __restrict__ in, float* __restrict__ out, size_t count) {
+  constexpr int E = 8;
+  const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * E;
+  if (i + E <= count && ((reinterpret_cast<uintptr_t>(in + i) & 15u) == 0)) {
+    float v[E];
+    unpack_raw<T, E>(v, ld_stream_u4(in + i));
+    st_stream_u4(out + i, make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3])));
+    st_stream_u4(out + i + 4, make_uint4(__float_as_uint(v[4]), __float_as_uint(v[5]), __float_as_uint(v[6]), __float_as_uint(v[7])));
+  } else {
+    for (size_t j = i; j < count && j < i + E; ++j) out[j] = Elem<T>::to_f(in[j]);
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) narrow_kernel(const float* __restrict__ in, T* __restrict__ out, size_t count) {
+  constexpr int E = 8;
+  const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * E;
+  if (i + E <= count && ((reinterpret_cast<uintptr_t>(out + i) & 15u) == 0)) {
+    const uint4 a = ld_stream_u4(in + i), b = ld_stream_u4(in + i + 4);
+    st_stream_u4(out + i, make_uint4(pack_pair<T>(__uint_as_float(a.x), __uint_as_float(a.y)),
+                                     pack_pair<T>(__uint_as_float(a.z), __uint_as_float(a.w)),
+                                     pack_pair<T>(__uint_as_float(b.x), __uint_as_float(b.y)),
+                                     pack_pair<T>(__uint_as_float(b.z), __uint_as_float(b.w))));
+  } else {
+    for (size_t j = i; j < count && j < i + E; ++j) out[j] = Elem<T>::from_f(in[j]);
+  }
+}
+template <typename T>
+static void widen(const T* in, float* out, size_t count, cudaStream_t stream) {
+  widen_kernel<T><<<(unsigned)((count + 2047) / 2048), 256, 0, stream>>>(in, out, count);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+template <typename T>
+static void narrow(const float* in, T* out, size_t count, cudaStream_t stream) {
+  narrow_kernel<T><<<(unsigned)((count + 2047) / 2048), 256, 0, stream>>>(in, out, count);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+constexpr size_t kWidenScratchLimit = size_t(2) << 30;   // fp32 scratch per call the widening path may take
+
+// The widening scratch is hundreds of MB per call: it comes from a pool of this library's own whose
+// release threshold keeps the memory across synchronisation points (the device's default pool hands
+// everything back at every synchronise, which made each call pay for fresh physical pages: +0.25 ms).
+static cudaError_t widen_scratch_alloc(void** p, size_t bytes, cudaStream_t stream) {
+  static cudaMemPool_t pools[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return cudaMallocAsync(p, bytes, stream);
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (pools[dev] == nullptr) {
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = dev;
+      cudaMemPool_t pool = nullptr;
+      if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return cudaMallocAsync(p, bytes, stream);
+      }
+      unsigned long long keep = kWidenScratchLimit;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      pools[dev] = pool;
+    }
+  }
+  return cudaMallocFromPoolAsync(p, bytes, pools[dev], stream);
+}
+
+static int spmm_core(tsp_plan* plan, int n, int replicas, int values_shared, const int* row_indices,
+                     const float* values, const int* value_perm_or_null, const float* dense,
+                     const float* bias_or_null, int relu, float* out, cudaStream_t stream);
+static int sddmm_core(tsp_plan* plan, int k, int replicas, const int* row_indices, const float* lhs,
+                      const float* rhs, float* out, cudaStream_t stream, bool reduce);
+
 template <typename T>
 static int spmm_b16(const char* name, tsp_plan* plan, int n, int replicas, int values_shared,
                     const int* row_indices, const void* values, const int* value_perm_or_null,
@@ -853,6 +935,33 @@ static int spmm_b16(const char* name, tsp_plan* plan, int n, int replicas, int v
     if (st > 1) return st - 1;
     if (st == 0) return TSP_OK;
   }
+  {
+    // the shapes the fp32 path gives to the staged (merged-row, FFMA2) kernel: widen, run it, narrow
+    SpmmArgs f;
+    f.m = m; f.k = k; f.n = n; f.nnz = nnz;
+    f.dense = reinterpret_cast<const float*>(uintptr_t(16)); f.out = reinterpret_cast<float*>(uintptr_t(16));   // (alignment probe only)
+    f.value_perm = value_perm_or_null;
+    const size_t nv = (size_t)nnz * (values_shared ? 1 : replicas), nd = (size_t)k * n * replicas, no = (size_t)m * n * replicas;
+    // (crossover measured at 4096^3 fp16: row-split 2.10 / 4.15 ms at density 0.25 / 0.5, widened 2.63 / 3.46 ms)
+    if (variant == 0 && a.guard_flag == nullptr && (double)nnz / ((double)m * k) >= 0.35 && spmm_staged_applicable(f, replicas) &&
+        (nv + nd + no) * 4 <= kWidenScratchLimit) {
+      float* scratch = nullptr;
+      cudaError_t e = widen_scratch_alloc(reinterpret_cast<void**>(&scratch), (nv + nd + no) * 4 + 768, stream);
+      if (e != cudaSuccess) return cuda_fail(e, name);
+      float* v32 = scratch;
+      float* d32 = v32 + ((nv + 63) & ~size_t(63));
+      float* o32 = d32 + ((nd + 63) & ~size_t(63));
+      widen<T>(a.values, v32, nv, stream);
+      widen<T>(a.dense, d32, nd, stream);
+      int rc = spmm_core(plan, n, replicas, values_shared, row_indices, v32, nullptr, d32, bias_or_null, relu, o32, stream);
+      if (rc == TSP_OK) {
+        narrow<T>(o32, a.out, no, stream);
+        if (cudaGetLastError() != cudaSuccess) rc = TSP_ERR_CUDA;
+      }
+      cudaFreeAsync(scratch, stream);
+      return rc;
+    }
+  }
   launch_spmm_rowsplit<T>(a, replicas, stream);   // (guarded fallback when a band launch is in front of it)
   TSP_CHECK_LAUNCH(name);
   return TSP_OK;
@@ -886,7 +995,37 @@ static int sddmm_b16(const char* name, tsp_plan* plan, int k, int replicas, cons
   }
   if (variant != 1 && sddmm_rows_applicable(a)) {
     launch_sddmm_rows<T>(a, replicas, stream);
-  } else if (k % 8 == 0 && aligned16(lhs) && aligned16(rhs)) {
+    TSP_CHECK_LAUNCH(name);
+    return TSP_OK;
+  }
+  {
+    // the shapes the fp32 path gives to the TMA-staged kernels (sampled / tiled): widen, run them, narrow
+    SddmmArgs f;
+    f.m = m; f.k = k; f.n = n; f.nnz = nnz;
+    f.lhs = reinterpret_cast<const float*>(uintptr_t(16)); f.rhs = f.lhs;   // (alignment probe only)
+    const double density = (double)nnz / ((double)m * (double)n);
+    const size_t nl = (size_t)m * k * replicas, nr = (size_t)n * k * replicas, no = (size_t)nnz * replicas;
+    const bool staged = (density >= 0.22 && sddmm_tiled_applicable(f, replicas)) ||
+                        (density >= 0.015 && sddmm_sampled_applicable(f, replicas));
+    if (variant == 0 && a.guard_flag == nullptr && staged && (nl + nr + no) * 4 <= kWidenScratchLimit) {
+      float* scratch = nullptr;
+      cudaError_t e = widen_scratch_alloc(reinterpret_cast<void**>(&scratch), (nl + nr + no) * 4 + 768, stream);
+      if (e != cudaSuccess) return cuda_fail(e, name);
+      float* l32 = scratch;
+      float* r32 = l32 + ((nl + 63) & ~size_t(63));
+      float* o32 = r32 + ((nr + 63) & ~size_t(63));
+      widen<T>(a.lhs, l32, nl, stream);
+      widen<T>(a.rhs, r32, nr, stream);
+      int rc = sddmm_core(plan, k, replicas, nullptr, l32, r32, o32, stream, false);
+      if (rc == TSP_OK) {
+        narrow<T>(o32, a.out, no, stream);
+        if (cudaGetLastError() != cudaSuccess) rc = TSP_ERR_CUDA;
+      }
+      cudaFreeAsync(scratch, stream);
+      return rc;
+    }
+  }
+  if (k % 8 == 0 && aligned16(lhs) && aligned16(rhs)) {
     if (k <= 64) launch_sddmm_gather<8, 8, T>(a, replicas, stream);
     else if (k <= 128) launch_sddmm_gather<8, 16, T>(a, replicas, stream);
     else launch_sddmm_gather<8, 32, T>(a, replicas, stream);
