@@ -293,6 +293,43 @@ __device__ __forceinline__ unsigned pack_pair<__nv_bfloat16>(float lo, float hi)
   return *reinterpret_cast<const unsigned*>(&h);
 }
 
+// Mixed-precision FMA (PTX fma.rn.f32.f16 / .bf16, SASS FHFMA[.BF16] on sm_100a): both factors are 16-bit
+// elements read straight out of a packed register half, the addend and the result are fp32, ONE
+// rounding -- bit-identical to widening both factors and an fp32 FMA, without the two conversion
+// instructions per element that made the 16-bit kernels issue-bound (profiles/r02_c4_sddmm_rows_f16_*).
+// acc += a.lo * b.lo + a.hi * b.hi over one packed pair, in that order.
+template <typename T>
+__device__ __forceinline__ float fma_pair_16(unsigned a, unsigned b, float acc);
+template <>
+__device__ __forceinline__ float fma_pair_16<__half>(unsigned a, unsigned b, float acc) {
+  asm("{\n.reg .b16 al, ah, bl, bh;\nmov.b32 {al, ah}, %1;\nmov.b32 {bl, bh}, %2;\n"
+      "fma.rn.f32.f16 %0, al, bl, %0;\nfma.rn.f32.f16 %0, ah, bh, %0;\n}"
+      : "+f"(acc) : "r"(a), "r"(b));
+  return acc;
+}
+template <>
+__device__ __forceinline__ float fma_pair_16<__nv_bfloat16>(unsigned a, unsigned b, float acc) {
+  asm("{\n.reg .b16 al, ah, bl, bh;\nmov.b32 {al, ah}, %1;\nmov.b32 {bl, bh}, %2;\n"
+      "fma.rn.f32.bf16 %0, al, bl, %0;\nfma.rn.f32.bf16 %0, ah, bh, %0;\n}"
+      : "+f"(acc) : "r"(a), "r"(b));
+  return acc;
+}
+// (acc0, acc1) += w * (x.lo, x.hi): one 16-bit factor `w` (low half of the register) against a packed pair.
+template <typename T>
+__device__ __forceinline__ void fma_scalar_pair_16(unsigned w, unsigned x, float& acc0, float& acc1);
+template <>
+__device__ __forceinline__ void fma_scalar_pair_16<__half>(unsigned w, unsigned x, float& acc0, float& acc1) {
+  asm("{\n.reg .b16 wl, wh, xl, xh;\nmov.b32 {wl, wh}, %2;\nmov.b32 {xl, xh}, %3;\n"
+      "fma.rn.f32.f16 %0, wl, xl, %0;\nfma.rn.f32.f16 %1, wl, xh, %1;\n}"
+      : "+f"(acc0), "+f"(acc1) : "r"(w), "r"(x));
+}
+template <>
+__device__ __forceinline__ void fma_scalar_pair_16<__nv_bfloat16>(unsigned w, unsigned x, float& acc0, float& acc1) {
+  asm("{\n.reg .b16 wl, wh, xl, xh;\nmov.b32 {wl, wh}, %2;\nmov.b32 {xl, xh}, %3;\n"
+      "fma.rn.f32.bf16 %0, wl, xl, %0;\nfma.rn.f32.bf16 %1, wl, xh, %1;\n}"
+      : "+f"(acc0), "+f"(acc1) : "r"(w), "r"(x));
+}
+
 // Raw register image of a vector load of BYTES bytes.
 template <int BYTES>
 struct RawVec;

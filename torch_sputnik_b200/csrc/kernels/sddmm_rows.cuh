@@ -52,9 +52,14 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT
   // this lane's chunk `sub` of rhs row 0 (16-byte units); chunk cc of row c is at + c * (8 * KC) + cc * 8
   const T* const rbase = a.rhs + (size_t)rep * a.n * K + sub * E;
   const T* const lrow = a.lhs + ((size_t)rep * a.m + row) * K + sub * E;
+  // fp32: lhs slices widened once; 16-bit: kept packed (4 registers per chunk) for the mixed-precision FMA
   float lv[KC][E];
+  uint4 lraw[KC];
 #pragma unroll
-  for (int cc = 0; cc < KC; ++cc) load_elems<T, E>(lv[cc], lrow + cc * 8 * E);
+  for (int cc = 0; cc < KC; ++cc) {
+    if constexpr (sizeof(T) == 4) load_elems<T, E>(lv[cc], lrow + cc * 8 * E);
+    else lraw[cc] = __ldg(reinterpret_cast<const uint4*>(lrow + cc * 8 * E));
+  }
   // Even and odd elements of the lane's chunks are summed separately as one packed fma.rn.f32x2
   // chain (half the issue slots), then added -- the SAME association as sddmm_band (band.cuh), so the
   // two kernels the heuristic chooses between for a short inner dimension agree bit for bit.
@@ -62,17 +67,17 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT
     float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int cc = 0; cc < KC; ++cc) {
-      float x[E];
-      load_elems<T, E>(x, rbase + ((size_t)o + cc * 8) * E);
+      if constexpr (sizeof(T) == 4) {
+        float x[E];
+        load_elems<T, E>(x, rbase + ((size_t)o + cc * 8) * E);
 #pragma unroll
-      for (int e = 0; e < E; e += 2) {
-        if constexpr (sizeof(T) == 4) {
-          ffma2(s0, s1, lv[cc][e], lv[cc][e + 1], x[e], x[e + 1]);
-        } else {   // 16-bit storage: one chain -- the unpacked pairs are not register-adjacent, packing them (2.08 ms)
-                   // or even splitting the chain in two (1.99 ms) costs more than it saves (1.90 ms at C4)
-          s0 = fmaf(lv[cc][e], x[e], s0);
-          s0 = fmaf(lv[cc][e + 1], x[e + 1], s0);
-        }
+        for (int e = 0; e < E; e += 2) ffma2(s0, s1, lv[cc][e], lv[cc][e + 1], x[e], x[e + 1]);
+      } else {   // 16-bit storage: one chain of mixed-precision FMAs over the packed pairs, ascending k
+        const uint4 x = __ldg(reinterpret_cast<const uint4*>(rbase + ((size_t)o + cc * 8) * E));
+        s0 = fma_pair_16<T>(lraw[cc].x, x.x, s0);
+        s0 = fma_pair_16<T>(lraw[cc].y, x.y, s0);
+        s0 = fma_pair_16<T>(lraw[cc].z, x.z, s0);
+        s0 = fma_pair_16<T>(lraw[cc].w, x.w, s0);
       }
     }
     return s0 + s1;

@@ -26,9 +26,10 @@
 
 namespace tsp {
 
-// (Measured and dropped: sending a 16-bit value and its column between lanes as ONE packed word --
-// one shuffle per step instead of two -- is slower, 2.51 vs 2.31 ms at the C4 shape: the unpacking
-// costs more issue slots than the shuffle it saves.  profiles/r02_band_ab.txt)
+// (Measured twice and dropped: sending a 16-bit value and its column between lanes as ONE packed word -- one
+// shuffle per step instead of two -- is slower both with widening FMAs (2.51 vs 2.31 ms at the C4 shape) and
+// with the mixed-precision FMA, where the value half needs no unpacking at all (2.19 vs 2.03 ms): the second
+// shuffle is not what the kernel waits for.  profiles/r02_band_ab.txt)
 template <typename T, int EPL, int LPN, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArgsT<T> a) {
   constexpr int G = 32 / LPN;
@@ -56,11 +57,16 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArg
   const int beg = __ldg(a.row_offsets + row), end = __ldg(a.row_offsets + row + 1);
   for (int base = beg; base < end; base += 32) {
     const int cnt = min(32, end - base);
+    // 16-bit storage with full vectors: the value travels between lanes as its raw 16 bits and meets the
+    // packed operand pairs in mixed-precision FMAs (no widening instructions)
+    constexpr bool MIXED = sizeof(T) == 2 && EPL == 8;
     float myval = 0.f;
     unsigned myoff = 0u;
     if (lane < cnt) {
       const int idx = base + lane;
-      myval = Elem<T>::to_f(vals[a.value_perm ? __ldg(a.value_perm + idx) : idx]);
+      const T raw = vals[a.value_perm ? __ldg(a.value_perm + idx) : idx];
+      if constexpr (MIXED) myval = __uint_as_float((unsigned)*reinterpret_cast<const unsigned short*>(&raw));
+      else myval = Elem<T>::to_f(raw);
       myoff = (unsigned)__ldg(cols + idx) * row_units;
     }
     // step g: group `grp` takes nonzero g * G + grp of the batch
@@ -81,10 +87,18 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArg
 #pragma unroll
       for (int u = 0; u < UNR; ++u)
         if (on[u]) {
-          float b[EPL];
-          unpack_raw<T, EPL>(b, raw[u]);
+          if constexpr (MIXED) {
+            const unsigned w = __float_as_uint(v[u]);
+            fma_scalar_pair_16<T>(w, raw[u].x, acc[0], acc[1]);
+            fma_scalar_pair_16<T>(w, raw[u].y, acc[2], acc[3]);
+            fma_scalar_pair_16<T>(w, raw[u].z, acc[4], acc[5]);
+            fma_scalar_pair_16<T>(w, raw[u].w, acc[6], acc[7]);
+          } else {
+            float b[EPL];
+            unpack_raw<T, EPL>(b, raw[u]);
 #pragma unroll
-          for (int e = 0; e < EPL; ++e) acc[e] = fmaf(v[u], b[e], acc[e]);
+            for (int e = 0; e < EPL; ++e) acc[e] = fmaf(v[u], b[e], acc[e]);
+          }
         }
     }
   }
