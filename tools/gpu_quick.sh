@@ -1,5 +1,9 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_f16.py tests/test_gpu_band.py tests/test_gpu_attention.py -q 2>&1 | tail -4
-timeout 600 python tools/ab_band.py 2>&1 | tail -1 | cut -c1-700
+for op in spmm sddmm; do
+TSP_DTYPE=f16 timeout 300 ncu --set full --clock-control none --profile-from-start off -c 1 -f -o gpurun_out/r02_c4_${op}_f16_mixed python tools/prof_c4.py $op 32 2 > /dev/null 2>&1
+python tools/ncu_summary.py gpurun_out/r02_c4_${op}_f16_mixed.ncu-rep > gpurun_out/r02_c4_${op}_f16_mixed_ncu_summary.txt
+grep -E "==|time_duration|registers_per|warps_active|lsu_wavefronts.avg|issue_active|pipe_fma_cycles|inst_executed.sum|long_scoreboard|short_scoreboard|wait_per|not_selected|l1tex__t_sector_hit|lts__t_sector|xbar2l1tex|lg_throttle|mio_throttle" gpurun_out/r02_c4_${op}_f16_mixed_ncu_summary.txt
+done
+rm -f gpurun_out/*.ncu-rep
