@@ -83,11 +83,15 @@ __global__ void __launch_bounds__(WARPS * 32) sddmm_rows_kernel(const SddmmArgsT
     return s0 + s1;
   };
 
+  // The column batch of the NEXT 32 nonzeros is requested one batch ahead: its latency (an L2 hit for a
+  // streamed index array) hides under this batch's gathers instead of heading every batch.
+  unsigned nextoff = beg + lane < end ? (unsigned)__ldg(cols + beg + lane) * (unsigned)(8 * KC) : 0u;
   for (int p = beg; p < end; p += 32) {
     const int cnt = min(32, end - p);
-    // rhs row offset of nonzero p + lane in float4 units (row 0 for the lanes past the row's end:
+    // rhs row offset of nonzero p + lane in 16-byte units (row 0 for the lanes past the row's end:
     // a valid address, the result is never stored)
-    const unsigned myoff = lane < cnt ? (unsigned)__ldg(cols + p + lane) * (unsigned)(8 * KC) : 0u;
+    const unsigned myoff = nextoff;
+    nextoff = p + 32 + lane < end ? (unsigned)__ldg(cols + p + 32 + lane) * (unsigned)(8 * KC) : 0u;
     float acc[8];
     if (cnt == 32) {
 #pragma unroll

@@ -55,20 +55,29 @@ __global__ void __launch_bounds__(WARPS * 32) spmm_rowsplit_kernel(const SpmmArg
   for (int e = 0; e < EPL; ++e) acc[e] = 0.f;
 
   const int beg = __ldg(a.row_offsets + row), end = __ldg(a.row_offsets + row + 1);
+  // 16-bit storage with full vectors: the value travels between lanes as its raw 16 bits and meets the
+  // packed operand pairs in mixed-precision FMAs (no widening instructions)
+  constexpr bool MIXED = sizeof(T) == 2 && EPL == 8;
+  // (value, offset) of nonzero idx for this lane; fetched one batch AHEAD so that the index / value latency
+  // hides under the current batch's gathers
+  float nextval = 0.f;
+  unsigned nextoff = 0u;
+  auto fetch = [&](int idx) {
+    nextval = 0.f;
+    nextoff = 0u;
+    if (idx < end) {
+      const T raw = vals[a.value_perm ? __ldg(a.value_perm + idx) : idx];
+      if constexpr (MIXED) nextval = __uint_as_float((unsigned)*reinterpret_cast<const unsigned short*>(&raw));
+      else nextval = Elem<T>::to_f(raw);
+      nextoff = (unsigned)__ldg(cols + idx) * row_units;
+    }
+  };
+  fetch(beg + lane);
   for (int base = beg; base < end; base += 32) {
     const int cnt = min(32, end - base);
-    // 16-bit storage with full vectors: the value travels between lanes as its raw 16 bits and meets the
-    // packed operand pairs in mixed-precision FMAs (no widening instructions)
-    constexpr bool MIXED = sizeof(T) == 2 && EPL == 8;
-    float myval = 0.f;
-    unsigned myoff = 0u;
-    if (lane < cnt) {
-      const int idx = base + lane;
-      const T raw = vals[a.value_perm ? __ldg(a.value_perm + idx) : idx];
-      if constexpr (MIXED) myval = __uint_as_float((unsigned)*reinterpret_cast<const unsigned short*>(&raw));
-      else myval = Elem<T>::to_f(raw);
-      myoff = (unsigned)__ldg(cols + idx) * row_units;
-    }
+    const float myval = nextval;
+    const unsigned myoff = nextoff;
+    fetch(base + 32 + lane);
     // step g: group `grp` takes nonzero g * G + grp of the batch
 #pragma unroll
     for (int g0 = 0; g0 < LPN; g0 += UNR) {
