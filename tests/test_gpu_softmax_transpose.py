@@ -83,6 +83,28 @@ def test_transpose_bit_exact(ops, dev, m, n, density):
         assert torch.equal(ops.permute_values(v, perm), vt)
 
 
+@pytest.mark.parametrize("m,n,density", [(3072, 768, 0.1), (768, 3072, 0.1), (1, 5000, 0.5), (9000, 48000, 0.0005), (2000, 30000, 0.05), (800, 49152, 0.15),
+                                         (2500, 1, 0.7), (257, 1025, 0.33)])
+def test_transpose_counting_and_radix_paths_agree(ops, dev, m, n, density):
+    """Both sorts behind csr_transpose (3-launch counting path, multi-pass radix path) against the oracle;
+    3072 x 768 at 10 % is the sparse linear layer of tests/test_left_spmm.py:101-154."""
+    a = random_csr(m, n, density, seed=7 * m + n, values="pm1")
+    v, _, ro, ci = to_dev(a, dev)
+    evt, erot, ecit, eperm = oracle.csr_transpose(m, n, a.values, a.row_offsets, a.column_indices)
+    ops.plan_policy(0)
+    try:
+        for variant in (0, 1):
+            ops.set_variant("transpose", variant)
+            vt, rot, cit, perm = ops.csr_transpose_with_perm(m, n, v, ro, ci)
+            np.testing.assert_array_equal(rot.cpu().numpy(), erot)
+            np.testing.assert_array_equal(cit.cpu().numpy(), ecit)
+            np.testing.assert_array_equal(vt.cpu().numpy(), evt)
+            np.testing.assert_array_equal(perm.cpu().numpy(), eperm)
+    finally:
+        ops.set_variant("transpose", 0)
+        ops.plan_policy(1)
+
+
 def test_transpose_known_answer_4x4_empty_first_row(ops, dev):
     """tests/test_transpose.py:27-32."""
     t = lambda a, dt: torch.tensor(a, dtype=dt, device=dev)

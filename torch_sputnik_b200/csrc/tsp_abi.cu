@@ -29,6 +29,7 @@ std::atomic<int> g_spmm_warps{0};
 std::atomic<int> g_sddmm_warps{0};
 std::atomic<int> g_attn_warps{0};
 std::atomic<int> g_band_warps{0};
+std::atomic<int> g_transpose_variant{0};
 std::atomic<int> g_spmm_scb{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_spmm_rowsplit_max_n{0};   // fp32 operands up to this many columns take spmm_rowsplit
@@ -83,6 +84,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "spmm_scb") == 0) return g_spmm_scb.exchange(variant);
   if (op && strcmp(op, "band_warps") == 0) return g_band_warps.exchange(variant);
   if (op && strcmp(op, "attn_warps") == 0) return g_attn_warps.exchange(variant);
+  if (op && strcmp(op, "transpose") == 0) return g_transpose_variant.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
@@ -625,10 +627,47 @@ static size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 size_t tsp_csr_transpose_workspace(int m, int n, int nnz) {
   (void)m;
   if (nnz < 0 || n < 0) return 0;
+  const int variant = g_transpose_variant.load();
+  const CountPlan c = make_count_plan(n, nnz, variant);
+  if (c.use && variant != 1) return align256(sizeof(int) * count_plan_ints(c, n)) + 256;
   const SortPlan p = make_sort_plan(n, nnz);
   // keys A/B, payload A/B, [radix][tiles] histogram
   return 4 * align256(sizeof(int) * (size_t)nnz) + align256(sizeof(int) * (size_t)p.radix * p.tiles) +
          256;
+}
+
+// benchmark knob "transpose" (g_transpose_variant): 1 = radix path always, k >= 2 = at most k * SMs chunks
+
+// Counting path: count -> offsets -> place (kernels/csr_transpose.cuh).
+static int transpose_counting(const CountPlan& c, int m, int n, int nnz, int replicas, const float* values,
+                              const int* row_offsets, const int* column_indices, float* values_t,
+                              int* row_offsets_t, int* column_indices_t, int* perm_or_null, void* workspace,
+                              cudaStream_t stream) {
+  int* table = static_cast<int*>(workspace);
+  int* chain = table + (size_t)c.chunks * n;
+  const size_t smem = sizeof(int) * (size_t)n;
+  if (smem > 48 * 1024) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+      cudaFuncSetAttribute(transpose_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)(sizeof(int) * kCountMaxCols));
+      cudaFuncSetAttribute(transpose_place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)(sizeof(int) * kCountMaxCols));
+    });
+  }
+  transpose_count_kernel<<<c.chunks, kCountThreads, smem, stream>>>(column_indices, n, nnz, c.chunk_len, table, chain,
+                                                                    64 + c.groups);
+  TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (count)");
+  transpose_offsets_kernel<<<c.groups, kCountGroupCols, 0, stream>>>(n, nnz, c.chunks, table, chain, row_offsets_t);
+  TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (offsets)");
+  TransposePlaceArgs a;
+  a.m = m; a.n = n; a.nnz = nnz; a.replicas = replicas; a.chunk_len = c.chunk_len;
+  a.row_offsets = row_offsets; a.column_indices = column_indices; a.values = values;
+  a.table = table; a.row_offsets_t = row_offsets_t;
+  a.values_t = values_t; a.column_indices_t = column_indices_t; a.perm = perm_or_null;
+  transpose_place_kernel<<<c.chunks, kCountThreads, smem, stream>>>(a);
+  TSP_CHECK_LAUNCH("tsp_csr_transpose_f32 (place)");
+  return TSP_OK;
 }
 
 int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* values,
@@ -654,6 +693,11 @@ int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* valu
   if ((reinterpret_cast<uintptr_t>(workspace) & 255u) != 0)
     return invalid("tsp_csr_transpose_f32: workspace must be 256-byte aligned");
 
+  const int variant = g_transpose_variant.load();
+  const CountPlan cp = make_count_plan(n, nnz, variant);
+  if (cp.use && variant != 1)
+    return transpose_counting(cp, m, n, nnz, replicas, values, row_offsets, column_indices, values_t, row_offsets_t,
+                              column_indices_t, perm_or_null, workspace, stream);
   const SortPlan p = make_sort_plan(n, nnz);
   char* ws = static_cast<char*>(workspace);
   const size_t seg = align256(sizeof(int) * (size_t)nnz);
