@@ -36,7 +36,9 @@ def test_argument_errors_do_not_need_a_gpu():
     assert rc == 1 and "negative" in cabi.last_error()
     rc = lib.tsp_sddmm_f32(4, 4, 4, 4, 70000, None, None, None, None, None, None, None)
     assert rc == 1 and "65535" in cabi.last_error()
-    assert lib.tsp_csr_transpose_workspace(4096, 4096, 1 << 20) >= 4 * 4 * (1 << 20)
+    # counting path: a [chunks][n] table of at most 4 ints per nonzero; radix path (wide matrix): 16 B per nonzero
+    assert 4 * 4096 <= lib.tsp_csr_transpose_workspace(4096, 4096, 1 << 20) <= 17 * (1 << 20)
+    assert lib.tsp_csr_transpose_workspace(512, 100000, 1 << 20) >= 4 * 4 * (1 << 20)
     plan = ctypes.c_void_p()
     rc = lib.tsp_plan_create(-1, 4, 0, None, None, None, ctypes.byref(plan))
     assert rc == 1 and plan.value is None and "negative" in cabi.last_error()
