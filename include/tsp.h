@@ -262,6 +262,11 @@ int tsp_permute_values_b16(int nnz, int replicas, const void* values, const int*
  * tsp_plan_spmm_f32 / tsp_plan_sddmm_f32: tsp_spmm_perm_f32 / tsp_sddmm_f32 (reduce == 0) /
  *   tsp_sddmm_reduce_f32 (reduce != 0) on the plan's topology; m, k (resp. m, n) and nnz come from the
  *   plan, `n` is the dense operand's column count (resp. `k` the inner dimension).
+ * tsp_plan_permute_values_f32 / _b16: values_t[r, p] = values[r, perm[p]] with the permutation of the
+ *   plan's transpose (built on first use, like tsp_plan_transpose) -- the value half of csr_transpose on a
+ *   static topology (src/transpose_cuda.cu:90-99 redoes the whole csr2csc per call).  Same result as
+ *   tsp_permute_values_f32 with that perm; large inputs go through a per-topology tiled view of the
+ *   permutation (sources of every output tile in ascending order) instead of a sector-per-element gather.
  */
 typedef struct tsp_plan tsp_plan;
 int tsp_plan_create(int m, int n, int nnz, const int* row_offsets, const int* column_indices,
@@ -283,6 +288,10 @@ int tsp_plan_spmm_b16(tsp_plan* plan, int bf16, int n, int replicas, int values_
                       void* stream);
 int tsp_plan_sddmm_b16(tsp_plan* plan, int bf16, int k, int replicas, const int* row_indices,
                        const void* lhs, const void* rhs, void* out, void* stream);
+int tsp_plan_permute_values_f32(tsp_plan* plan, int replicas, const float* values, float* values_t,
+                                void* stream);
+int tsp_plan_permute_values_b16(tsp_plan* plan, int replicas, const void* values, void* values_t,
+                                void* stream);
 
 /*
  * Knobs for A/B benchmarking only (not part of the reference surface):

@@ -285,3 +285,26 @@ def test_planned_ops_inside_a_cuda_graph(ops, dev):
     torch.cuda.synchronize()
     for g, w in zip(got, want):
         assert torch.equal(g, w)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m,n,density,r", [(1024, 1536, 0.1, 5), (700, 300, 0.6, 33), (2048, 2048, 0.05, 1)])
+def test_planned_transpose_values_tiled_view_equals_gather(ops, dev, m, n, density, r, dtype):
+    """csr_transpose on a cached topology moves the values through the plan's tiled permutation view (large
+    inputs) or the plain gather: both equal values[:, perm] exactly, for a last tile that is not full too."""
+    a = random_csr(m, n, density, seed=m + n, values="pm1")
+    assert a.nnz > 2 * 32768 and a.nnz % 32768 != 0
+    ro = torch.from_numpy(a.row_offsets).to(dev)
+    ci = torch.from_numpy(a.column_indices).to(dev)
+    v = torch.rand((r, a.nnz), device=dev).to(dtype)
+    _, _, eperm = oracle.csr_transpose(m, n, a.values, a.row_offsets, a.column_indices)[1:]
+    ref = v[:, torch.from_numpy(eperm).to(dev).long()]
+    try:
+        for knob in (2, 1, 0):
+            ops.set_variant("permute_tiled", knob)
+            vt, rot, cit, perm = ops.csr_transpose_with_perm(m, n, v, ro, ci)
+            assert torch.equal(vt, ref), knob
+            assert torch.equal(ops.permute_values(v, perm), ref), knob
+            assert torch.equal(ops.permute_values(v[0], perm), ref[0]), knob
+    finally:
+        ops.set_variant("permute_tiled", 0)

@@ -18,6 +18,7 @@ SYMBOLS = (
     "tsp_plan_sddmm_f32",
     "tsp_spmm_f16", "tsp_spmm_bf16", "tsp_sddmm_f16", "tsp_sddmm_bf16", "tsp_csr_softmax_f16", "tsp_csr_softmax_bf16",
     "tsp_permute_values_b16", "tsp_plan_spmm_b16", "tsp_plan_sddmm_b16",
+    "tsp_plan_permute_values_f32", "tsp_plan_permute_values_b16",
     "tsp_sparse_attention_supported_b16", "tsp_sparse_attention_b16",
     "tsp_sddmm_many_f32", "tsp_spmm_many_f32", "tsp_csr_softmax_many_f32", "tsp_permute_values_many_f32",
 )
@@ -71,6 +72,8 @@ def load() -> ctypes.CDLL:
         lib.tsp_plan_sddmm_f32.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp]
         lib.tsp_plan_spmm_b16.argtypes = [vp, i, i, i, i, vp, vp, vp, vp, vp, i, vp, vp]
         lib.tsp_plan_sddmm_b16.argtypes = [vp, i, i, i, vp, vp, vp, vp, vp]
+        lib.tsp_plan_permute_values_f32.argtypes = [vp, i, vp, vp, vp]
+        lib.tsp_plan_permute_values_b16.argtypes = [vp, i, vp, vp, vp]
         _lib = lib
     return _lib
 

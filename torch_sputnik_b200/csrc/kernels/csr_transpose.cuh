@@ -10,6 +10,9 @@
 // per-warp counters.  A last kernel turns the sorted order into values_t / column_indices_t /
 // row_offsets_t / perm.
 #pragma once
+#include <atomic>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace tsp {
@@ -376,15 +379,141 @@ __global__ void __launch_bounds__(kCountThreads) transpose_place_kernel(const Tr
 // V: float, or unsigned short for any 16-bit storage type (a pure move).
 // masks.prefix != null: many masks in one launch -- replica blockIdx.y uses perm + prefix[mask] (indices LOCAL
 // to the mask) and the ragged value layout of MaskTable; nnz is then the largest mask's count.
-template <typename V>
-__global__ void __launch_bounds__(256)
+// A CTA moves a RUN of ITEMS * blockDim consecutive outputs.  The permutation of a transpose walks the
+// output column by column, so the 32-byte sector holding values[row, c .. c+7] is wanted again one output
+// row (= one column's worth of nonzeros) later: with a long run per CTA that second request finds the
+// sector in this SM's L1 instead of fetching it from L2 once per element.
+template <typename V, int ITEMS>
+__global__ void __launch_bounds__(1024)
 permute_values_kernel(int nnz, const V* __restrict__ values, const int* __restrict__ perm,
                       V* __restrict__ values_t, const MaskTable masks) {
-  const int p = blockIdx.x * 256 + threadIdx.x;
   const MaskView mv = mask_view(masks, blockIdx.y, nnz);
-  if (p >= mv.nnz) return;
-  const size_t base = (size_t)mv.values;
-  values_t[base + p] = __ldg(values + base + __ldg(perm + mv.cols + p));
+  const int run = ITEMS * blockDim.x;
+  const int p0 = blockIdx.x * run + threadIdx.x;
+  if (p0 - (int)threadIdx.x >= mv.nnz) return;
+  const V* __restrict__ src = values + (size_t)mv.values;
+  V* __restrict__ dst = values_t + (size_t)mv.values;
+  const int* __restrict__ pm = perm + mv.cols;
+  int idx[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i) {
+    const int p = p0 + i * blockDim.x;
+    idx[i] = p < mv.nnz ? __ldg(pm + p) : -1;
+  }
+  V v[ITEMS];
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i)
+    if (idx[i] >= 0) v[i] = __ldg(src + idx[i]);
+#pragma unroll
+  for (int i = 0; i < ITEMS; ++i)
+    if (idx[i] >= 0) dst[p0 + i * blockDim.x] = v[i];
+}
+
+extern std::atomic<int> g_permute_cfg;   // benchmark knob "permute": 100 * items + threads / 32 (0 = default)
+
+template <typename V>
+inline void launch_permute_values(int nnz, int replicas, const V* values, const int* perm, V* values_t,
+                                  const MaskTable& masks, cudaStream_t stream) {
+  int cfg = g_permute_cfg.load();
+  if (cfg <= 0) cfg = nnz >= (1 << 16) ? 816 : 108;
+  const int items = cfg / 100, threads = (cfg % 100) * 32;
+  const dim3 grid(ceil_div(nnz, items * threads), replicas);
+  switch (items) {
+    case 1: permute_values_kernel<V, 1><<<grid, threads, 0, stream>>>(nnz, values, perm, values_t, masks); break;
+    case 2: permute_values_kernel<V, 2><<<grid, threads, 0, stream>>>(nnz, values, perm, values_t, masks); break;
+    case 4: permute_values_kernel<V, 4><<<grid, threads, 0, stream>>>(nnz, values, perm, values_t, masks); break;
+    case 16: permute_values_kernel<V, 16><<<grid, threads, 0, stream>>>(nnz, values, perm, values_t, masks); break;
+    default: permute_values_kernel<V, 8><<<grid, threads, 0, stream>>>(nnz, values, perm, values_t, masks); break;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tiled permutation view (plans): the gather above asks L2 for one 32-byte sector per 4-byte value --
+// the request rate, not the bytes, is what bounds it (C4: 0.77 ms for 1.7 GB).  For a cached transpose
+// the outputs are cut into tiles of kPermTile consecutive positions and, once per topology, each tile's
+// elements are listed in ASCENDING SOURCE order (one stable radix pass over the tile id of the inverse
+// permutation).  A tile of a transpose covers a block of columns, so in that order the sources form one
+// short contiguous run per matrix row: neighbouring threads read neighbouring values, drop them into the
+// tile's slot in shared memory, and the tile leaves as fully coalesced stores.
+constexpr int kPermTileBits = 15;
+constexpr int kPermTile = 1 << kPermTileBits;     // outputs per tile (128 KB of fp32 in shared memory)
+constexpr int kPermThreads = 1024;
+constexpr int kPermItems = kPermTile / kPermThreads;
+
+__global__ void __launch_bounds__(256) inverse_perm_kernel(int nnz, const int* __restrict__ perm, int* __restrict__ inv) {
+  const int p = blockIdx.x * 256 + threadIdx.x;
+  if (p < nnz) inv[__ldg(perm + p)] = p;
+}
+
+// sorted_dst / sorted_src: the (destination, source) pairs ordered by (tile of destination, source)
+__global__ void __launch_bounds__(256)
+perm_view_finish_kernel(int nnz, const int* __restrict__ sorted_dst, const int* __restrict__ sorted_src,
+                        int* __restrict__ view_src, unsigned short* __restrict__ view_loc) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= nnz) return;
+  view_src[j] = __ldg(sorted_src + j);
+  view_loc[j] = (unsigned short)(__ldg(sorted_dst + j) & (kPermTile - 1));
+}
+
+template <typename V>
+__global__ void __launch_bounds__(kPermThreads, 1)
+permute_tiled_kernel(int nnz, int replicas, int reps_per_cta, const V* __restrict__ values,
+                     const int* __restrict__ view_src, const unsigned short* __restrict__ view_loc,
+                     V* __restrict__ values_t) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  V* const s_tile = reinterpret_cast<V*>(s_raw);
+  const int t0 = blockIdx.x * kPermTile;
+  const int cnt = min(kPermTile, nnz - t0);
+  int src[kPermItems];
+  unsigned loc[kPermItems / 2];
+#pragma unroll
+  for (int i = 0; i < kPermItems; i += 2) {
+    const int j0 = i * kPermThreads + threadIdx.x, j1 = j0 + kPermThreads;
+    src[i] = j0 < cnt ? __ldg(view_src + t0 + j0) : -1;
+    src[i + 1] = j1 < cnt ? __ldg(view_src + t0 + j1) : -1;
+    const unsigned l0 = j0 < cnt ? __ldg(view_loc + t0 + j0) : 0u;
+    const unsigned l1 = j1 < cnt ? __ldg(view_loc + t0 + j1) : 0u;
+    loc[i / 2] = l0 | (l1 << 16);
+  }
+  const int r0 = blockIdx.y * reps_per_cta, r1 = min(replicas, r0 + reps_per_cta);
+  for (int r = r0; r < r1; ++r) {
+    const V* __restrict__ vin = values + (size_t)r * nnz;
+    V* __restrict__ vout = values_t + (size_t)r * nnz + t0;
+#pragma unroll
+    for (int b = 0; b < kPermItems; b += 8) {
+      V v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (src[b + i] >= 0) v[i] = __ldg(vin + src[b + i]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (src[b + i] >= 0) s_tile[(loc[(b + i) / 2] >> (16 * ((b + i) & 1))) & 0xffffu] = v[i];
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int i = 0; i < kPermItems; ++i) {
+      const int j = i * kPermThreads + threadIdx.x;
+      if (j < cnt) vout[j] = s_tile[j];
+    }
+    __syncthreads();
+  }
+}
+
+template <typename V>
+inline int launch_permute_tiled(int nnz, int replicas, const V* values, const int* view_src,
+                                const unsigned short* view_loc, V* values_t, cudaStream_t stream) {
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(permute_tiled_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)(kPermTile * sizeof(V)));
+  });
+  const int tiles = ceil_div(nnz, kPermTile);
+  int reps = (int)(((long long)tiles * replicas) / (4LL * sm_count()));
+  reps = reps < 1 ? 1 : (reps > 16 ? 16 : reps);
+  const dim3 grid(tiles, ceil_div(replicas, reps));
+  permute_tiled_kernel<V><<<grid, kPermThreads, kPermTile * sizeof(V), stream>>>(nnz, replicas, reps, values, view_src,
+                                                                                  view_loc, values_t);
+  return 0;
 }
 
 __global__ void fill_int_kernel(int* __restrict__ dst, int count, int value) {

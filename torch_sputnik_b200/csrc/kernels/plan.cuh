@@ -50,6 +50,8 @@ struct tsp_plan {
   int* ro_t = nullptr;
   int* ci_t = nullptr;
   int* perm = nullptr;               // values_t[p] = values[perm[p]]
+  int* pv_src = nullptr;             // tiled view of perm (csr_transpose.cuh): sources of every output tile in
+  unsigned short* pv_loc = nullptr;  // ascending order + their slot inside the tile; null for small topologies
   cudaEvent_t ev_t = nullptr;
   cudaStream_t t_stream = nullptr;
   bool t_settled = false;
@@ -229,6 +231,8 @@ inline void plan_destroy(tsp_plan* p) {
   if (p->ro_t) cudaFree(p->ro_t);
   if (p->ci_t) cudaFree(p->ci_t);
   if (p->perm) cudaFree(p->perm);
+  if (p->pv_src) cudaFree(p->pv_src);
+  if (p->pv_loc) cudaFree(p->pv_loc);
   if (p->ev_t) cudaEventDestroy(p->ev_t);
   if (p->d_flag) cudaFree(p->d_flag);
   if (p->h_flag) cudaFreeHost(p->h_flag);

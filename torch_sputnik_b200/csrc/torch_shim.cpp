@@ -127,6 +127,9 @@ using PlanKey = std::tuple<const void*, const void*, int64_t, int64_t, int64_t>;
 struct PlanCache {
   std::mutex mu;
   std::map<PlanKey, std::shared_ptr<PlanEntry>> entries;
+  // perm array of a planned transpose -> owner of the plan it belongs to (the array is the plan's own device
+  // memory, so while the owner lives the address cannot mean anything else)
+  std::map<const void*, std::weak_ptr<PlanHolder>> by_perm;
   uint64_t tick = 0, hits = 0, misses = 0, evictions = 0;
   int policy = 1;        // 0: never plan (every call takes the unplanned C-ABI entry), 1: plan on first sight
   size_t capacity = 256;
@@ -244,6 +247,9 @@ void ensure_transposed(const std::shared_ptr<PlanEntry>& e, int64_t m, int64_t n
   ce->nnz = count;
   ce->tick = ++c.tick;
   c.entries[PlanKey{ro_t, ci_t, n, m, count}] = ce;
+  for (auto it = c.by_perm.begin(); it != c.by_perm.end();)
+    it = it->second.expired() ? c.by_perm.erase(it) : std::next(it);
+  c.by_perm[perm] = e->holder;
   evict_locked(c);
 }
 
@@ -497,7 +503,42 @@ torch::Tensor sparse_softmax_backward(torch::Tensor y, torch::Tensor dy, torch::
   return dx;
 }
 
+// values[..., perm] with the permutation of a planned transpose (tiled view for large inputs).
+static torch::Tensor plan_permute_values_impl(tsp_plan* plan, const torch::Tensor& values) {
+  torch::Tensor out = torch::empty_like(values);
+  const int replicas = values.dim() == 2 ? (int)values.size(0) : 1;
+  if (values.scalar_type() != torch::kFloat32)
+    check_rc(tsp_plan_permute_values_b16(plan, replicas, values.data_ptr(), out.data_ptr(), current_stream()),
+             "permute_values");
+  else
+    check_rc(tsp_plan_permute_values_f32(plan, replicas, values.data_ptr<float>(), out.data_ptr<float>(),
+                                         current_stream()),
+             "permute_values");
+  return out;
+}
+
+static torch::Tensor permute_values_plain(const torch::Tensor& values, const torch::Tensor& perm);
+
 static torch::Tensor permute_values_impl(const torch::Tensor& values, const torch::Tensor& perm) {
+  {
+    // the perm of a cached transpose (ops.transposed_topology / csr_transpose_with_perm): take its plan
+    PlanCache& c = plan_cache();
+    std::shared_ptr<PlanHolder> owner;
+    {
+      std::lock_guard<std::mutex> lock(c.mu);
+      auto it = c.by_perm.find(perm.data_ptr());
+      if (it != c.by_perm.end()) {
+        owner = it->second.lock();
+        if (!owner) c.by_perm.erase(it);
+      }
+    }
+    if (owner && perm._version() == 0 && !current_stream_capturing())
+      return plan_permute_values_impl(owner->plan, values);
+  }
+  return permute_values_plain(values, perm);
+}
+
+static torch::Tensor permute_values_plain(const torch::Tensor& values, const torch::Tensor& perm) {
   torch::Tensor out = torch::empty_like(values);
   const int replicas = values.dim() == 2 ? (int)values.size(0) : 1;
   if (values.scalar_type() != torch::kFloat32)
@@ -538,7 +579,10 @@ static std::vector<torch::Tensor> transpose_impl(int m, int n, const torch::Tens
   if (nnz > 0) {
     if (auto e = get_plan(m, n, row_offsets, column_indices)) {
       ensure_transposed(e, m, n, values.device());
-      std::vector<torch::Tensor> out{permute_values_impl(values, e->perm), e->ro_t, e->ci_t};
+      // (under CUDA-graph capture: the plain gather, which asks the plan nothing)
+      std::vector<torch::Tensor> out{current_stream_capturing() ? permute_values_plain(values, e->perm)
+                                                                : plan_permute_values_impl(e->plan, values),
+                                     e->ro_t, e->ci_t};
       if (want_perm) out.push_back(e->perm);
       return out;
     }

@@ -30,6 +30,8 @@ std::atomic<int> g_sddmm_warps{0};
 std::atomic<int> g_attn_warps{0};
 std::atomic<int> g_band_warps{0};
 std::atomic<int> g_transpose_variant{0};
+std::atomic<int> g_permute_cfg{0};
+std::atomic<int> g_permute_tiled{0};
 std::atomic<int> g_spmm_scb{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_spmm_rowsplit_max_n{0};   // fp32 operands up to this many columns take spmm_rowsplit
@@ -85,6 +87,8 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "band_warps") == 0) return g_band_warps.exchange(variant);
   if (op && strcmp(op, "attn_warps") == 0) return g_attn_warps.exchange(variant);
   if (op && strcmp(op, "transpose") == 0) return g_transpose_variant.exchange(variant);
+  if (op && strcmp(op, "permute") == 0) return g_permute_cfg.exchange(variant);
+  if (op && strcmp(op, "permute_tiled") == 0) return g_permute_tiled.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
@@ -122,6 +126,48 @@ void tsp_plan_destroy(tsp_plan* plan) { plan_destroy(plan); }
 
 int tsp_plan_sorted(tsp_plan* plan) { return plan ? plan_sorted_state(plan) : -1; }
 
+// Tiled view of plan->perm for tsp_plan_permute_values_* (kernels/csr_transpose.cuh): the pairs
+// (destination, source) in order of (tile of destination, source) = a stable radix sort of the inverse
+// permutation by its tile bits.  Queued behind the transpose on the same stream; topologies smaller than
+// two tiles keep the plain gather.
+static int build_permutation_view(tsp_plan* plan, cudaStream_t stream) {
+  const int nnz = plan->nnz;
+  if (nnz < 2 * kPermTile) return TSP_OK;
+  const SortPlan sp = make_sort_plan(ceil_div(nnz, kPermTile), nnz);
+  const size_t seg = (sizeof(int) * (size_t)nnz + 255) & ~size_t(255);
+  char* ws = nullptr;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&ws), 5 * seg + sizeof(int) * (size_t)sp.radix * sp.tiles + 256);
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&plan->pv_src), sizeof(int) * (size_t)nnz);
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&plan->pv_loc), sizeof(unsigned short) * (size_t)nnz);
+  if (e != cudaSuccess) {   // no view: the gather still works
+    (void)cudaGetLastError();
+    cudaFree(ws); cudaFree(plan->pv_src); cudaFree(plan->pv_loc);
+    plan->pv_src = nullptr; plan->pv_loc = nullptr;
+    return TSP_OK;
+  }
+  int* inv = reinterpret_cast<int*>(ws);
+  int* keys[2] = {reinterpret_cast<int*>(ws + seg), reinterpret_cast<int*>(ws + 2 * seg)};
+  int* pay[2] = {reinterpret_cast<int*>(ws + 3 * seg), reinterpret_cast<int*>(ws + 4 * seg)};
+  int* hist = reinterpret_cast<int*>(ws + 5 * seg);
+  inverse_perm_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(nnz, plan->perm, inv);
+  const int* kin = inv;
+  const int* pin = nullptr;
+  for (int pass = 0; pass < sp.passes; ++pass) {
+    const int shift = kPermTileBits + pass * sp.digit_bits;
+    radix_hist_kernel<<<sp.tiles, kSortThreads, 0, stream>>>(kin, nnz, shift, sp.radix, sp.tiles, hist);
+    exclusive_scan_kernel<<<1, 1024, 0, stream>>>(hist, sp.radix * sp.tiles);
+    radix_scatter_kernel<<<sp.tiles, kSortThreads, 0, stream>>>(kin, pin, nnz, shift, sp.radix, sp.tiles, hist,
+                                                              keys[pass & 1], pay[pass & 1]);
+    kin = keys[pass & 1];
+    pin = pay[pass & 1];
+  }
+  perm_view_finish_kernel<<<ceil_div(nnz, 256), 256, 0, stream>>>(nnz, kin, pin, plan->pv_src, plan->pv_loc);
+  const cudaError_t le = cudaGetLastError();
+  cudaFree(ws);   // waits for the kernels above
+  if (le != cudaSuccess) return cuda_fail(le, "tsp_plan_transpose (permutation view)");
+  return TSP_OK;
+}
+
 int tsp_plan_transpose(tsp_plan* plan, void* stream_, tsp_plan** transposed_out, const int** row_offsets_t,
                        const int** column_indices_t, const int** perm) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -149,6 +195,7 @@ int tsp_plan_transpose(tsp_plan* plan, void* stream_, tsp_plan** transposed_out,
       rc = tsp_plan_create(n, m, nnz, plan->ro_t, plan->ci_t, stream_, &t);
       plan->transposed = t;
     }
+    if (rc == TSP_OK) rc = build_permutation_view(plan, stream);
     if (rc == TSP_OK) {
       plan->t_stream = stream;
       if (cudaEventCreateWithFlags(&plan->ev_t, cudaEventDisableTiming) != cudaSuccess ||
@@ -743,8 +790,7 @@ int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int
   if (replicas > 65535) return invalid("tsp_permute_values_f32: replicas=%d exceeds 65535", replicas);
   if (nnz == 0 || replicas == 0) return TSP_OK;
   if (!values || !perm || !values_t) return invalid("tsp_permute_values_f32: null pointer argument");
-  dim3 grid(ceil_div(nnz, 256), replicas);
-  permute_values_kernel<float><<<grid, 256, 0, stream>>>(nnz, values, perm, values_t, MaskTable{});
+  launch_permute_values<float>(nnz, replicas, values, perm, values_t, MaskTable{}, stream);
   TSP_CHECK_LAUNCH("tsp_permute_values_f32");
   return TSP_OK;
 }
@@ -756,11 +802,49 @@ int tsp_permute_values_b16(int nnz, int replicas, const void* values, const int*
   if (replicas > 65535) return invalid("tsp_permute_values_b16: replicas=%d exceeds 65535", replicas);
   if (nnz == 0 || replicas == 0) return TSP_OK;
   if (!values || !perm || !values_t) return invalid("tsp_permute_values_b16: null pointer argument");
-  dim3 grid(ceil_div(nnz, 256), replicas);
-  permute_values_kernel<unsigned short><<<grid, 256, 0, stream>>>(
-      nnz, static_cast<const unsigned short*>(values), perm, static_cast<unsigned short*>(values_t), MaskTable{});
+  launch_permute_values<unsigned short>(nnz, replicas, static_cast<const unsigned short*>(values), perm,
+                                        static_cast<unsigned short*>(values_t), MaskTable{}, stream);
   TSP_CHECK_LAUNCH("tsp_permute_values_b16");
   return TSP_OK;
+}
+
+// values_t[r, p] = values[r, perm[p]] with the permutation of the plan's cached transpose: the tiled view
+// when the plan has one and there is enough to move, else the plain gather.
+// benchmark knob "permute_tiled" (g_permute_tiled): 1 = never, 2 = whenever a view exists
+}  // extern "C"
+
+template <typename V>
+static int plan_permute_values(const char* name, tsp_plan* plan, int replicas, const V* values, V* values_t,
+                               void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (!plan || plan->ephemeral) return invalid("%s: needs a plan from tsp_plan_create", name);
+  if (replicas < 0) return invalid("%s: negative replicas", name);
+  if (replicas > 65535) return invalid("%s: replicas=%d exceeds 65535", name, replicas);
+  const int* perm = nullptr;
+  const int rc = tsp_plan_transpose(plan, stream_, nullptr, nullptr, nullptr, &perm);
+  if (rc != TSP_OK) return rc;
+  const int nnz = plan->nnz;
+  if (nnz == 0 || replicas == 0) return TSP_OK;
+  if (!values || !values_t) return invalid("%s: null pointer argument", name);
+  const int knob = g_permute_tiled.load();
+  const bool tiled = plan->pv_src != nullptr && knob != 1 &&
+                     (knob == 2 || (long long)nnz * replicas >= (1LL << 21));
+  if (tiled) launch_permute_tiled<V>(nnz, replicas, values, plan->pv_src, plan->pv_loc, values_t, stream);
+  else launch_permute_values<V>(nnz, replicas, values, perm, values_t, MaskTable{}, stream);
+  TSP_CHECK_LAUNCH(name);
+  return TSP_OK;
+}
+
+extern "C" {
+
+int tsp_plan_permute_values_f32(tsp_plan* plan, int replicas, const float* values, float* values_t, void* stream) {
+  return plan_permute_values<float>("tsp_plan_permute_values_f32", plan, replicas, values, values_t, stream);
+}
+
+int tsp_plan_permute_values_b16(tsp_plan* plan, int replicas, const void* values, void* values_t, void* stream) {
+  return plan_permute_values<unsigned short>("tsp_plan_permute_values_b16", plan, replicas,
+                                             static_cast<const unsigned short*>(values),
+                                             static_cast<unsigned short*>(values_t), stream);
 }
 
 // ----------------------------------------------------------------- many masks in one launch
@@ -852,8 +936,7 @@ int tsp_permute_values_many_f32(int b, int heads, int max_nnz, const int* nnz_pr
   MaskTable t;
   t.prefix = nnz_prefix;
   t.heads = heads;
-  dim3 grid(ceil_div(max_nnz, 256), b * heads);
-  permute_values_kernel<float><<<grid, 256, 0, stream>>>(max_nnz, values, perm, values_t, t);
+  launch_permute_values<float>(max_nnz, b * heads, values, perm, values_t, t, stream);
   TSP_CHECK_LAUNCH("tsp_permute_values_many_f32");
   return TSP_OK;
 }
