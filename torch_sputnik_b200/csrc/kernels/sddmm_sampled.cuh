@@ -27,6 +27,7 @@
 // 16-byte aligned operands.
 #pragma once
 #include <algorithm>
+#include <type_traits>
 #include "sddmm_tiled.cuh"
 
 namespace tsp {
@@ -88,17 +89,41 @@ __device__ __forceinline__ float dot4(const float4& l, const float4& r, float ac
 
 // NB_LO: batches (of 4 slots) executed unconditionally -- straight-line code the scheduler can
 // software-pipeline across; the host derives it from the expected tile population minus 4 sigma.
-template <class Cfg, int NB_LO>
+// 16-bit storage: a row's 128-byte slab holds 64 elements and stays PACKED in registers; every pair of
+// elements goes through the mixed-precision FMA (fma.rn.f32.f16 / .bf16, fp32 accumulator), so one LDS.128
+// feeds 8 multiply-adds instead of 4 -- the shared-memory bound of this kernel doubles.
+template <typename T>
+__device__ __forceinline__ float dot_slab16(const uint4& l, const uint4& r, float acc) {
+  acc = fma_pair_16<T>(l.x, r.x, acc);
+  acc = fma_pair_16<T>(l.y, r.y, acc);
+  acc = fma_pair_16<T>(l.z, r.z, acc);
+  return fma_pair_16<T>(l.w, r.w, acc);
+}
+template <typename T>
+__device__ __forceinline__ float dot_slab(const uint4& l, const uint4& r, float acc) {
+  if constexpr (sizeof(T) == 4) {
+    acc = fmaf(__uint_as_float(l.x), __uint_as_float(r.x), acc);
+    acc = fmaf(__uint_as_float(l.y), __uint_as_float(r.y), acc);
+    acc = fmaf(__uint_as_float(l.z), __uint_as_float(r.z), acc);
+    return fmaf(__uint_as_float(l.w), __uint_as_float(r.w), acc);
+  } else {
+    return dot_slab16<T>(l, r, acc);
+  }
+}
+__device__ __forceinline__ uint4 lds_u4(const unsigned char* p) { return *reinterpret_cast<const uint4*>(p); }
+
+template <class Cfg, int NB_LO, typename T = float>
 __global__ void __launch_bounds__(Cfg::THREADS, 2)
-sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
+sddmm_sampled_kernel(const SddmmArgsT<T> a, const StagedGuard guard, int nb, int bn,
                      const int* __restrict__ starts, const __grid_constant__ CUtensorMap tm_lhs,
                      const __grid_constant__ CUtensorMap tm_rhs, const int ksplit) {
-  constexpr int BM = Cfg::BM, BK = Cfg::BK, P = Cfg::P, STAGES = Cfg::STAGES, CAP = Cfg::CAP;
+  constexpr int BM = Cfg::BM, P = Cfg::P, STAGES = Cfg::STAGES, CAP = Cfg::CAP;
+  constexpr int BK = Cfg::BK * 4 / (int)sizeof(T);   // elements in a 128-byte slab row
   if (staged_declines(guard)) return;
 
   extern __shared__ unsigned char smem_dyn[];
   unsigned char* const smem_raw = smem_dyn + ((128u - (smem_u32(smem_dyn) & 127u)) & 127u);
-  const int stage_bytes = (BM + bn) * BK * 4;
+  const int stage_bytes = (BM + bn) * 128;
   unsigned char* const ring = smem_raw;
   unsigned* const ent = reinterpret_cast<unsigned*>(ring + (size_t)STAGES * stage_bytes);
   int* const oidx = reinterpret_cast<int*>(ent + CAP);
@@ -169,7 +194,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
   if (total == 0) return;
 
   const int* __restrict__ cols = a.column_indices;
-  float* __restrict__ out = a.out + ((size_t)rep * ksplit + blockIdx.z) * a.nnz;
+  T* __restrict__ out = a.out + ((size_t)rep * ksplit + blockIdx.z) * a.nnz;
   const int c0 = cb * bn;
   int q = 0, q_base = 0;  // slabs consumed so far by this CTA (ring position carries across rounds)
 
@@ -217,7 +242,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
       const int ks = kq % ksteps1, rr = a.reduce_reps > 0 ? kq / ksteps1 : rep;
       mbar_arrive_expect_tx(full + st, (unsigned)stage_bytes);
       tma_load_3d(dst, &tm_lhs, ks * BK, rb * BM, rr, full + st);
-      tma_load_3d(dst + BM * BK * 4, &tm_rhs, ks * BK, c0, rr, full + st);
+      tma_load_3d(dst + BM * 128, &tm_rhs, ks * BK, c0, rr, full + st);
     };
     const int q_end = q + ksteps;
     if (tid == 0)
@@ -230,25 +255,25 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
       // Plain shared loads (not asm): the mbarrier asm statements carry memory clobbers, so the
       // compiler keeps these between the wait and the arrive but is free to pipeline them.
       const unsigned char* const sl = ring + (size_t)st * stage_bytes + sub * 16;  // lhs rows
-      const unsigned char* const sr = sl + BM * BK * 4;                             // rhs rows
-      float4 l = make_float4(0.f, 0.f, 0.f, 0.f);
+      const unsigned char* const sr = sl + BM * 128;                                // rhs rows
+      uint4 l = make_uint4(0u, 0u, 0u, 0u);
       uint4 u = my4[0];
 #pragma unroll
       for (int b = 0; b < P / 4; ++b) {
         if (b < NB_LO || b < nbatch) {
           const uint4 uc = u;
           if (b + 1 < P / 4) u = my4[(b + 1 < NB_LO || b + 1 < nbatch) ? b + 1 : 0];
-          const float4 r0 = lds_f4(sr + (uc.x >> 12)), r1 = lds_f4(sr + (uc.y >> 12));
-          const float4 r2 = lds_f4(sr + (uc.z >> 12)), r3 = lds_f4(sr + (uc.w >> 12));
+          const uint4 r0 = lds_u4(sr + (uc.x >> 12)), r1 = lds_u4(sr + (uc.y >> 12));
+          const uint4 r2 = lds_u4(sr + (uc.z >> 12)), r3 = lds_u4(sr + (uc.w >> 12));
           const unsigned fw = (4 * b < 32) ? f_lo : f_hi;
-          if ((fw >> ((4 * b + 0) & 31)) & 1u) l = lds_f4(sl + ((uc.x & 0xfffu) << 4));
-          acc[4 * b + 0] = dot4(l, r0, acc[4 * b + 0]);
-          if ((fw >> ((4 * b + 1) & 31)) & 1u) l = lds_f4(sl + ((uc.y & 0xfffu) << 4));
-          acc[4 * b + 1] = dot4(l, r1, acc[4 * b + 1]);
-          if ((fw >> ((4 * b + 2) & 31)) & 1u) l = lds_f4(sl + ((uc.z & 0xfffu) << 4));
-          acc[4 * b + 2] = dot4(l, r2, acc[4 * b + 2]);
-          if ((fw >> ((4 * b + 3) & 31)) & 1u) l = lds_f4(sl + ((uc.w & 0xfffu) << 4));
-          acc[4 * b + 3] = dot4(l, r3, acc[4 * b + 3]);
+          if ((fw >> ((4 * b + 0) & 31)) & 1u) l = lds_u4(sl + ((uc.x & 0xfffu) << 4));
+          acc[4 * b + 0] = dot_slab<T>(l, r0, acc[4 * b + 0]);
+          if ((fw >> ((4 * b + 1) & 31)) & 1u) l = lds_u4(sl + ((uc.y & 0xfffu) << 4));
+          acc[4 * b + 1] = dot_slab<T>(l, r1, acc[4 * b + 1]);
+          if ((fw >> ((4 * b + 2) & 31)) & 1u) l = lds_u4(sl + ((uc.z & 0xfffu) << 4));
+          acc[4 * b + 2] = dot_slab<T>(l, r2, acc[4 * b + 2]);
+          if ((fw >> ((4 * b + 3) & 31)) & 1u) l = lds_u4(sl + ((uc.w & 0xfffu) << 4));
+          acc[4 * b + 3] = dot_slab<T>(l, r3, acc[4 * b + 3]);
         }
       }
       __syncwarp();
@@ -265,7 +290,7 @@ sddmm_sampled_kernel(const SddmmArgs a, const StagedGuard guard, int nb, int bn,
         for (int i = 0; i < 8; ++i) v[i] = acc[b * 8 + i];
         transpose_reduce<8>(v, sub);
         const int j = oidx[grp * P + b * 8 + sub];
-        if (j >= 0) out[j] = v[0];
+        if (j >= 0) out[j] = Elem<T>::from_f(v[0]);
       }
     }
     __syncthreads();  // ent/oidx are rewritten by the next round
@@ -284,6 +309,26 @@ inline bool encode_rowmajor_map_plain(CUtensorMap* tm, const float* base, int re
   return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// the same for 16-bit elements: box = [1][box_rows][64 elements] (128 bytes per row again)
+inline bool encode_rowmajor_map_plain_b16(CUtensorMap* tm, const void* base, bool bf16, int replicas, int rows, int k,
+                                          int box_rows) {
+  TensorMapEncodeFn enc = tensor_map_encoder();
+  if (!enc) return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)k, (cuuint64_t)rows, (cuuint64_t)replicas};
+  const cuuint64_t strides[2] = {(cuuint64_t)k * 2, (cuuint64_t)rows * k * 2};
+  const cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return enc(tm, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base),
+             dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <typename T>
+inline bool encode_sampled_map(CUtensorMap* tm, const T* base, int replicas, int rows, int k, int box_rows) {
+  if constexpr (sizeof(T) == 4) return encode_rowmajor_map_plain(tm, base, replicas, rows, k, box_rows);
+  else return encode_rowmajor_map_plain_b16(tm, base, std::is_same<T, __nv_bfloat16>::value, replicas, rows, k, box_rows);
 }
 
 inline bool sddmm_sampled_applicable(const SddmmArgs& a, int replicas) {
@@ -316,43 +361,46 @@ inline int build_sddmm_sampled_view(const int* row_offsets, const int* column_in
   return 0;
 }
 
-template <class Cfg, int NB_LO>
-inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_t stream,
+template <class Cfg, int NB_LO, typename T>
+inline int launch_sddmm_sampled_nb(const SddmmArgsT<T>& a, int replicas, cudaStream_t stream,
                                    const StagedGuard& guard, int bn, const int* starts) {
+  constexpr int BKE = Cfg::BK * 4 / (int)sizeof(T);   // elements per slab row
   const int row_blocks = ceil_div(a.m, Cfg::BM), nb = ceil_div(a.n, bn);
   const size_t smem = Cfg::smem_bytes(bn);
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 64 && !configured[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(sddmm_sampled_kernel<Cfg, NB_LO>,
+    cudaError_t e = cudaFuncSetAttribute(sddmm_sampled_kernel<Cfg, NB_LO, T>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes(256));
     if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (sampled smem attribute)");
     configured[dev] = true;
   }
   CUtensorMap tm_lhs, tm_rhs;
-  if (!encode_rowmajor_map_plain(&tm_lhs, a.lhs, replicas, a.m, a.k, Cfg::BM) ||
-      !encode_rowmajor_map_plain(&tm_rhs, a.rhs, replicas, a.n, a.k, bn)) {
+  if (!encode_sampled_map<T>(&tm_lhs, a.lhs, replicas, a.m, a.k, Cfg::BM) ||
+      !encode_sampled_map<T>(&tm_rhs, a.rhs, replicas, a.n, a.k, bn)) {
     set_error("tsp_sddmm_f32: cuTensorMapEncodeTiled failed");
     return 2;
   }
   const int grid_reps = a.reduce_reps > 0 ? 1 : replicas;
   // Split-K when the mask has fewer tiles than the GPU has CTA slots (sparse-linear weight
   // gradients of small layers: a 512 x 512 mask is 16 tiles): every CTA keeps >= 8 slabs.
-  const int ksteps_all = ceil_div(a.k, Cfg::BK) * (a.reduce_reps > 0 ? a.reduce_reps : 1);
+  const int ksteps_all = ceil_div(a.k, BKE) * (a.reduce_reps > 0 ? a.reduce_reps : 1);
   const long long tiles = (long long)row_blocks * nb * grid_reps;
-  const int ksplit = sddmm_sampled_ksplit(tiles, grid_reps, ksteps_all);
-  SddmmArgs b = a;
-  float* partial = nullptr;
+  // (16-bit outputs: no split-K -- the partial sums would have to stay fp32; the caller sends such shapes
+  // through the widened fp32 path instead)
+  const int ksplit = sizeof(T) == 4 ? sddmm_sampled_ksplit(tiles, grid_reps, ksteps_all) : 1;
+  SddmmArgsT<T> b = a;
+  T* partial = nullptr;
   if (ksplit > 1) {
-    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&partial), sizeof(float) * (size_t)ksplit * a.nnz, stream);
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&partial), sizeof(T) * (size_t)ksplit * a.nnz, stream);
     if (e != cudaSuccess) return cuda_fail(e, "tsp_sddmm_f32 (split-K scratch)");
     b.out = partial;
   }
   dim3 grid(row_blocks * nb, grid_reps, ksplit);
-  sddmm_sampled_kernel<Cfg, NB_LO><<<grid, Cfg::THREADS, smem, stream>>>(b, guard, nb, bn, starts, tm_lhs, tm_rhs, ksplit);
+  sddmm_sampled_kernel<Cfg, NB_LO, T><<<grid, Cfg::THREADS, smem, stream>>>(b, guard, nb, bn, starts, tm_lhs, tm_rhs, ksplit);
   TSP_CHECK_LAUNCH("tsp_sddmm_f32 (sampled)");
-  if (ksplit > 1) {
+  if constexpr (sizeof(T) == 4) if (ksplit > 1) {
     // (with unsorted columns the sampled kernel exits and this sums garbage; the guarded gather
     // fallback queued behind by the caller then rewrites every element of out)
     reduce_replicas_kernel<<<ceil_div(a.nnz, 256), 256, 0, stream>>>(partial, a.nnz, ksplit, a.out);
@@ -362,18 +410,18 @@ inline int launch_sddmm_sampled_nb(const SddmmArgs& a, int replicas, cudaStream_
   return 0;
 }
 
-template <class Cfg>
-inline int launch_sddmm_sampled_cfg(const SddmmArgs& a, int replicas, cudaStream_t stream,
+template <class Cfg, typename T>
+inline int launch_sddmm_sampled_cfg(const SddmmArgsT<T>& a, int replicas, cudaStream_t stream,
                                     const StagedGuard& guard, int bn, const int* starts) {
   // Batches every tile is expected to fill: (mu - 4 sigma) / 32 slots per group, 4 slots per batch.
   const double density = (double)a.nnz / ((double)a.m * (double)a.n);
   const double mu = (double)Cfg::BM * bn * density;
   const double lo = mu - 4.0 * sqrt(mu);
   const int nb_lo = lo > 0 ? (int)(lo / Cfg::GROUPS) / 4 : 0;
-  if (nb_lo >= 12 && Cfg::P >= 48) return launch_sddmm_sampled_nb<Cfg, 12>(a, replicas, stream, guard, bn, starts);
-  if (nb_lo >= 8) return launch_sddmm_sampled_nb<Cfg, 8>(a, replicas, stream, guard, bn, starts);
-  if (nb_lo >= 4) return launch_sddmm_sampled_nb<Cfg, 4>(a, replicas, stream, guard, bn, starts);
-  return launch_sddmm_sampled_nb<Cfg, 0>(a, replicas, stream, guard, bn, starts);
+  if (nb_lo >= 12 && Cfg::P >= 48) return launch_sddmm_sampled_nb<Cfg, 12, T>(a, replicas, stream, guard, bn, starts);
+  if (nb_lo >= 8) return launch_sddmm_sampled_nb<Cfg, 8, T>(a, replicas, stream, guard, bn, starts);
+  if (nb_lo >= 4) return launch_sddmm_sampled_nb<Cfg, 4, T>(a, replicas, stream, guard, bn, starts);
+  return launch_sddmm_sampled_nb<Cfg, 0, T>(a, replicas, stream, guard, bn, starts);
 }
 
 // Tile width: among the multiples of 8 columns (<= 256, <= n) whose expected nonzero count plus
@@ -422,10 +470,31 @@ inline int sddmm_sampled_pick_bn(const SddmmArgs& a, int replicas, int bn_overri
 }
 
 // Returns 0 / an error code.  `starts` is the block-start view for width bn (from the plan).
-inline int launch_sddmm_sampled(const SddmmArgs& a, int replicas, cudaStream_t stream, const StagedGuard& guard,
+template <typename T>
+inline int launch_sddmm_sampled(const SddmmArgsT<T>& a, int replicas, cudaStream_t stream, const StagedGuard& guard,
                                 int bn, const int* starts, int p_override = 0) {
-  if (p_override == 48) return launch_sddmm_sampled_cfg<SddmmSampledCfg<48, 2>>(a, replicas, stream, guard, bn, starts);
-  return launch_sddmm_sampled_cfg<SddmmSampledCfg<56, 2>>(a, replicas, stream, guard, bn, starts);
+  if constexpr (sizeof(T) == 4) {
+    if (p_override == 48)
+      return launch_sddmm_sampled_cfg<SddmmSampledCfg<48, 2>, T>(a, replicas, stream, guard, bn, starts);
+  }
+  return launch_sddmm_sampled_cfg<SddmmSampledCfg<56, 2>, T>(a, replicas, stream, guard, bn, starts);
+}
+
+// 16-bit storage: the shape the native sampled kernel takes (no split-K, no replica sum) and the
+// "shape-only" fp32 arguments its tile-width model is asked with: a slab holds 64 elements, so the kernel
+// sees half as many slabs as the fp32 one does for the same k.
+template <typename T>
+inline bool sddmm_sampled_b16_applicable(const SddmmArgsT<T>& a, int replicas, SddmmArgs* shape) {
+  if (a.reduce_reps > 0 || a.k % 8 != 0 || a.k < 512) return false;
+  if (!aligned16(a.lhs) || !aligned16(a.rhs)) return false;
+  if (a.m < 128 || a.n < 64) return false;
+  if (2.0 * a.nnz * a.k * replicas < 5.0e7) return false;
+  shape->m = a.m; shape->n = a.n; shape->nnz = a.nnz; shape->k = a.k / 2;
+  shape->lhs = shape->rhs = nullptr; shape->out = nullptr;
+  shape->row_offsets = a.row_offsets; shape->column_indices = a.column_indices;
+  const int bn = sddmm_sampled_pick_bn(*shape, replicas);
+  const long long tiles = (long long)ceil_div(a.m, 128) * ceil_div(a.n, bn) * replicas;
+  return sddmm_sampled_ksplit(tiles, replicas, ceil_div(a.k, 64)) == 1;
 }
 
 }  // namespace tsp

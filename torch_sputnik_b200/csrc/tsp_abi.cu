@@ -32,6 +32,10 @@ std::atomic<int> g_band_warps{0};
 std::atomic<int> g_transpose_variant{0};
 std::atomic<int> g_permute_cfg{0};
 std::atomic<int> g_permute_tiled{0};
+std::atomic<int> g_sddmm_b16{0};
+// 16-bit SDDMM: native sampled kernel below this density, widened fp32 tiled kernel above
+// (4096^3: 2.70 vs 2.96 ms at 35 %, 3.76 vs 2.96 at 50 %)
+constexpr double kSddmmB16SampledMaxDensity = 0.4;
 std::atomic<int> g_spmm_scb{0};
 static std::atomic<int> g_sddmm_variant{0};
 static std::atomic<int> g_spmm_rowsplit_max_n{0};   // fp32 operands up to this many columns take spmm_rowsplit
@@ -89,6 +93,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "transpose") == 0) return g_transpose_variant.exchange(variant);
   if (op && strcmp(op, "permute") == 0) return g_permute_cfg.exchange(variant);
   if (op && strcmp(op, "permute_tiled") == 0) return g_permute_tiled.exchange(variant);
+  if (op && strcmp(op, "sddmm_b16") == 0) return g_sddmm_b16.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
@@ -1071,7 +1076,7 @@ static int spmm_b16(const char* name, tsp_plan* plan, int n, int replicas, int v
     const size_t nv = (size_t)nnz * (values_shared ? 1 : replicas), nd = (size_t)k * n * replicas, no = (size_t)m * n * replicas;
     // (crossover measured at 4096^3 fp16: row-split 2.10 / 4.15 ms at density 0.25 / 0.5, widened 2.63 / 3.46 ms)
     if (variant == 0 && a.guard_flag == nullptr && (double)nnz / ((double)m * k) >= 0.35 && spmm_staged_applicable(f, replicas) &&
-        (nv + nd + no) * 4 <= kWidenScratchLimit) {
+        plan_sorted_state(plan, stream, true) != 0 && (nv + nd + no) * 4 <= kWidenScratchLimit) {
       float* scratch = nullptr;
       cudaError_t e = widen_scratch_alloc(reinterpret_cast<void**>(&scratch), (nv + nd + no) * 4 + 768, stream);
       if (e != cudaSuccess) return cuda_fail(e, name);
@@ -1126,6 +1131,33 @@ static int sddmm_b16(const char* name, tsp_plan* plan, int k, int replicas, cons
     return TSP_OK;
   }
   {
+    // Below the density where dense register tiles win: the sampled kernel on the 16-bit operands themselves
+    // (TMA-staged 128-byte slabs of 64 elements, packed operands into the mixed-precision FMA).
+    SddmmArgs shape;
+    const double density = (double)nnz / ((double)m * (double)n);
+    const int b16_variant = g_sddmm_b16.load();   // benchmark knob "sddmm_b16": 1 = never, 2 = at any density
+    if ((variant == 0 || variant == 3) && b16_variant != 1 && density >= 0.015 &&
+        (density < kSddmmB16SampledMaxDensity || b16_variant == 2 || variant == 3) &&
+        sddmm_sampled_b16_applicable(a, replicas, &shape)) {
+      StagedGuard guard;
+      int rc = 0;
+      const int gs = plan_guard(plan, stream, &guard, &rc);
+      if (rc != 0) return rc;
+      if (gs != kGuardUnsorted) {
+        const int bn = sddmm_sampled_pick_bn(shape, replicas);
+        const void* view = plan_view(plan, bn, stream, &rc);
+        if (rc != 0) return rc;
+        if (view) {
+          if ((rc = plan_flush_check(plan, stream)) != 0) return rc;
+          rc = launch_sddmm_sampled<T>(a, replicas, stream, guard, bn, static_cast<const int*>(view));
+          if (rc != 0) return rc;
+          if (gs == kGuardSorted) return TSP_OK;
+          a.guard_flag = guard.flag;   // columns not known sorted: the guarded gather kernel below redoes the work
+        }
+      }
+    }
+  }
+  if (a.guard_flag == nullptr) {
     // the shapes the fp32 path gives to the TMA-staged kernels (sampled / tiled): widen, run them, narrow
     SddmmArgs f;
     f.m = m; f.k = k; f.n = n; f.nnz = nnz;
@@ -1134,7 +1166,9 @@ static int sddmm_b16(const char* name, tsp_plan* plan, int k, int replicas, cons
     const size_t nl = (size_t)m * k * replicas, nr = (size_t)n * k * replicas, no = (size_t)nnz * replicas;
     const bool staged = (density >= 0.22 && sddmm_tiled_applicable(f, replicas)) ||
                         (density >= 0.015 && sddmm_sampled_applicable(f, replicas));
-    if (variant == 0 && a.guard_flag == nullptr && staged && (nl + nr + no) * 4 <= kWidenScratchLimit) {
+    // (columns known unsorted: no staged kernel would run on the widened copy either -- straight to the gather)
+    if (variant == 0 && a.guard_flag == nullptr && staged && plan_sorted_state(plan, stream, true) != 0 &&
+        (nl + nr + no) * 4 <= kWidenScratchLimit) {
       float* scratch = nullptr;
       cudaError_t e = widen_scratch_alloc(reinterpret_cast<void**>(&scratch), (nl + nr + no) * 4 + 768, stream);
       if (e != cudaSuccess) return cuda_fail(e, name);
