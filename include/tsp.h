@@ -176,6 +176,25 @@ int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* valu
                           int* perm_or_null, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/*
+ * tsp_csr_transpose_noalloc_f32: tsp_csr_transpose_f32 for callers that cannot allocate.  It has no counterpart in
+ * the reference (whose binding cudaMallocs a cuSPARSE buffer on every call, src/transpose_cuda.cu:22-43): it was
+ * added for code under CUDA-graph capture, tight serving loops and harnesses
+ * that forbid cudaMalloc.  Neither the caller nor the library allocates: the sort's scratch is a static device
+ * array of TSP_NOALLOC_SCRATCH_BYTES inside the library, held by every GPU that loads it until the process exits.
+ *   Same arguments, results and stable order as tsp_csr_transpose_f32, minus the workspace.
+ *   Limit: tsp_csr_transpose_workspace(m, n, nnz) <= TSP_NOALLOC_SCRATCH_BYTES (e.g. any 4096 x 4096 topology of up
+ *   to ~2 M nonzeros); larger problems return TSP_ERR_WORKSPACE with a message naming the need and the limit.
+ *   Calls no cudaMalloc / cudaFree / stream-ordered allocator.  All calls share the one array, which keeps the last
+ *   call's contents (the kernels initialise everything they read): calls whose kernels may overlap on the GPU --
+ *   different streams without ordering between them -- race on it; order them.
+ */
+#define TSP_NOALLOC_SCRATCH_BYTES (8u << 20)
+int tsp_csr_transpose_noalloc_f32(int m, int n, int nnz, int replicas, const float* values,
+                                  const int* row_offsets, const int* column_indices,
+                                  float* values_t, int* row_offsets_t, int* column_indices_t,
+                                  int* perm_or_null, void* stream);
+
 /* values_t[r, p] = values[r, perm[p]] for a cached permutation (static topology). */
 int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int* perm,
                            float* values_t, void* stream);

@@ -1,5 +1,7 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_f16.py tests/test_gpu_sddmm.py tests/test_gpu_plans.py tests/test_gpu_sharding.py -q -x 2>&1 | tail -8
-timeout 600 python tools/ab_sddmm_f16.py 2>&1 | tee gpurun_out/r02_sddmm_f16_ab.txt
+echo "== alone, fresh process"
+timeout 600 python -m pytest tests/test_zz_no_alloc.py -q -x -m gpu 2>&1 | tail -4
+echo "== after the whole GPU suite"
+timeout 2400 python -m pytest tests -q -x -m gpu 2>&1 | tail -6

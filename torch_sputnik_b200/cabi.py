@@ -18,7 +18,7 @@ SYMBOLS = (
     "tsp_plan_sddmm_f32",
     "tsp_spmm_f16", "tsp_spmm_bf16", "tsp_sddmm_f16", "tsp_sddmm_bf16", "tsp_csr_softmax_f16", "tsp_csr_softmax_bf16",
     "tsp_permute_values_b16", "tsp_plan_spmm_b16", "tsp_plan_sddmm_b16",
-    "tsp_plan_permute_values_f32", "tsp_plan_permute_values_b16",
+    "tsp_plan_permute_values_f32", "tsp_plan_permute_values_b16", "tsp_csr_transpose_noalloc_f32",
     "tsp_sparse_attention_supported_b16", "tsp_sparse_attention_b16",
     "tsp_sddmm_many_f32", "tsp_spmm_many_f32", "tsp_csr_softmax_many_f32", "tsp_permute_values_many_f32",
 )
@@ -44,6 +44,7 @@ def load() -> ctypes.CDLL:
         lib.tsp_csr_transpose_workspace.argtypes = [i, i, i]
         lib.tsp_csr_transpose_workspace.restype = sz
         lib.tsp_csr_transpose_f32.argtypes = [i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
+        lib.tsp_csr_transpose_noalloc_f32.argtypes = [i, i, i, i, vp, vp, vp, vp, vp, vp, vp, vp]
         lib.tsp_permute_values_f32.argtypes = [i, i, vp, vp, vp, vp]
         lib.tsp_sparse_attention_supported.argtypes = [i, i]
         lib.tsp_sparse_attention_f32.argtypes = [i, i, i, i, i, f, vp, vp, vp, vp, vp, vp, vp, vp, vp]

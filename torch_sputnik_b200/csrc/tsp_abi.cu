@@ -788,6 +788,55 @@ int tsp_csr_transpose_f32(int m, int n, int nnz, int replicas, const float* valu
   return TSP_OK;
 }
 
+// ---- csr_transpose without any allocation by anyone: the scratch is a file-scope device array ----
+// (no counterpart in the reference; added for callers that cannot call
+// cudaMalloc: CUDA-graph capture, tight serving loops, harnesses that forbid it).  Every GPU that loads the
+// library holds these TSP_NOALLOC_SCRATCH_BYTES until the process exits.  All calls share the array and it keeps
+// the last call's contents: the kernels write every word of it they later read (the count table, the chained-scan
+// words, the radix histograms and key / payload buffers), so nothing has to start at zero; two calls whose
+// kernels overlap on the GPU (different streams, no ordering) race on it.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[TSP_NOALLOC_SCRATCH_BYTES];
+
+// Device address of g_noalloc_scratch on the CURRENT device (in host code the array's name is only a host-side
+// stand-in): looked up once per device with that device current.
+static int noalloc_scratch_address(void** out) {
+  static void* cached[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "tsp_csr_transpose_noalloc_f32 (cudaGetDevice)");
+  if (dev < 0 || dev >= 64) return invalid("tsp_csr_transpose_noalloc_f32: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+      return cuda_fail(e != cudaSuccess ? e : cudaErrorInvalidSymbol, "tsp_csr_transpose_noalloc_f32 (cudaGetSymbolAddress)");
+    cached[dev] = ptr;
+  }
+  *out = cached[dev];
+  return TSP_OK;
+}
+
+int tsp_csr_transpose_noalloc_f32(int m, int n, int nnz, int replicas, const float* values,
+                                  const int* row_offsets, const int* column_indices, float* values_t,
+                                  int* row_offsets_t, int* column_indices_t, int* perm_or_null, void* stream_) {
+  if (m < 0 || n < 0 || nnz < 0 || replicas < 0)
+    return invalid("tsp_csr_transpose_noalloc_f32: negative dimension");
+  const size_t need = tsp_csr_transpose_workspace(m, n, nnz);
+  if (need > (size_t)TSP_NOALLOC_SCRATCH_BYTES) {
+    set_error("tsp_csr_transpose_noalloc_f32: this problem (m=%d n=%d nnz=%d) needs %zu bytes of scratch, more than "
+              "the %zu-byte static array; use tsp_csr_transpose_f32 with a caller-supplied workspace",
+              m, n, nnz, need, (size_t)TSP_NOALLOC_SCRATCH_BYTES);
+    return TSP_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  const int rc = noalloc_scratch_address(&scratch);
+  if (rc != TSP_OK) return rc;
+  return tsp_csr_transpose_f32(m, n, nnz, replicas, values, row_offsets, column_indices, values_t, row_offsets_t,
+                               column_indices_t, perm_or_null, scratch, (size_t)TSP_NOALLOC_SCRATCH_BYTES, stream_);
+}
+
 int tsp_permute_values_f32(int nnz, int replicas, const float* values, const int* perm,
                            float* values_t, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
