@@ -16,6 +16,8 @@ for d in 0.05 0.1 0.25 0.5; do
   cap r02_c2_spmm_d$tag python tools/prof_case.py spmm $d 2
   cap r02_c2_sddmm_d$tag python tools/prof_case.py sddmm $d 2
 done
+TSP_DTYPE=f16 cap r02_c2_sddmm_f16_d100 python tools/prof_case.py sddmm 0.1 2
+TSP_DTYPE=f16 cap r02_c2_spmm_f16_d100 python tools/prof_case.py spmm 0.1 2
 cap r02_c4_sddmm_band python tools/prof_c4.py sddmm 32 2
 TSP_VARIANT=5 cap r02_c4_sddmm_rows python tools/prof_c4.py sddmm 32 2
 cap r02_c4_spmm_gather python tools/prof_c4.py spmm 32 2
@@ -24,4 +26,4 @@ TSP_DTYPE=f16 cap r02_c4_sddmm_rows_f16 python tools/prof_c4.py sddmm 32 2
 TSP_DTYPE=f16 cap r02_c4_spmm_rowsplit_f16 python tools/prof_c4.py spmm 32 2
 python tools/ncu_traffic.py gpurun_out gpurun_out > gpurun_out/traffic.log 2>&1; tail -3 gpurun_out/traffic.log
 rm -f gpurun_out/r02_c2_*.ncu-rep gpurun_out/r02_c4_spmm*.ncu-rep gpurun_out/r02_c4_softmax.ncu-rep gpurun_out/r02_c4_sddmm_rows*.ncu-rep
-ls gpurun_out | head -50
+tools/ubench/bin/ubench_lds_pred > gpurun_out/r02_ubench_lds_pred.txt 2>&1; cat gpurun_out/r02_ubench_lds_pred.txt

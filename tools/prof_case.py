@@ -27,6 +27,9 @@ t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev)
 v, ri, ro, ci = t(a.values), t(a.row_indices), t(a.row_offsets), t(a.column_indices)
 b = t(dense_operand((dim, n), 1, "pm1"))
 lhs, rhs = t(dense_operand((dim, n), 2, "pm1")), t(dense_operand((dim, n), 3, "pm1"))
+if os.environ.get("TSP_DTYPE") in ("f16", "bf16"):   # 16-bit storage, fp32 arithmetic
+    dt = torch.float16 if os.environ["TSP_DTYPE"] == "f16" else torch.bfloat16
+    v, b, lhs, rhs = v.to(dt), b.to(dt), lhs.to(dt), rhs.to(dt)
 
 
 def call():
