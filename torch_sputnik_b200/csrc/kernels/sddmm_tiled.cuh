@@ -291,7 +291,7 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
 
   float* __restrict__ out = a.out + (size_t)rep * a.nnz;
 
-  auto issue = [&](int q) {   // warp 0, all lanes converge here
+  auto issue = [&](int q) {   // one warp (q & 3 of the step it runs in), all lanes converge here
     const int st = q % STAGES, use = q / STAGES;
     if (use > 0) mbar_wait(empty + st, (use - 1) & 1);
     if (lane == 0) {
@@ -336,7 +336,11 @@ sddmm_tiled2_kernel(const SddmmArgs a, const StagedGuard guard, int tiles_per_ct
       for (int j = 0; j < 8; ++j) acc[i][j] = 0ull;
 
     for (int ks = 0; ks < ksteps; ++ks, ++q) {
-      if (warp == 0 && q + AHEAD < Q) issue(q + AHEAD);
+      // The producer role rotates over the warps: with one fixed producer warp its extra work (the wait on
+      // `empty`, the two TMA issues) made it the slowest, the other three ran ahead until they were blocked on
+      // the slab it had not requested yet, and from then on took the full TMA latency at every slab (measured:
+      // 63 % of the waits on `full` found the phase incomplete and lasted 715 cycles; rotating: 0.1 %).
+      if (warp == (q & 3) && q + AHEAD < Q) issue(q + AHEAD);
       const int st = q % STAGES;
       mbar_wait(full + st, (q / STAGES) & 1);
       const char* const sbase = reinterpret_cast<const char*>(ring + st * C::kStageFloats);
