@@ -1,5 +1,8 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-for d in 0.25 0.5; do python tools/prof_case.py spmm $d 5 | tail -1; done
-python tools/prof_case.py sddmm 0.5 5 | tail -1
+timeout 900 python -m pytest tests/test_gpu_sddmm.py tests/test_gpu_f16.py tests/test_gpu_plans.py tests/test_gpu_sharding.py tests/test_gpu_modules.py -q -x 2>&1 | tail -2
+for d in 0.02 0.05 0.1 0.15 0.2; do
+  python tools/prof_case.py sddmm $d 5 | tail -1
+  TSP_DTYPE=f16 python tools/prof_case.py sddmm $d 5 | tail -1
+done

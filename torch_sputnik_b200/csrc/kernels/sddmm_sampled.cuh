@@ -38,7 +38,7 @@ struct SddmmSampledCfg {
   static constexpr int P = P_, STAGES = STAGES_;
   static constexpr int CAP = GROUPS * P_;
   static size_t smem_bytes(int bn) {
-    return (size_t)STAGES_ * (BM + bn) * BK * 4 + (size_t)CAP * 8 + BM * 4 + (BM + 1) * 4 + 2 * GROUPS * 4 + 2 * STAGES_ * 8 + 256;
+    return (size_t)STAGES_ * (BM + bn) * BK * 4 + (size_t)CAP * 8 + BM * 4 + (BM + 1) * 4 + BM * 4 + 2 * GROUPS * 4 + 2 * STAGES_ * 8 + 256;
   }
 };
 
@@ -128,8 +128,9 @@ sddmm_sampled_kernel(const SddmmArgsT<T> a, const StagedGuard guard, int nb, int
   unsigned* const ent = reinterpret_cast<unsigned*>(ring + (size_t)STAGES * stage_bytes);
   int* const oidx = reinterpret_cast<int*>(ent + CAP);
   int* const row_start = oidx + CAP;       // [BM]   flat index of the row's first nonzero in the tile
-  int* const row_off = row_start + BM;     // [BM+1] exclusive prefix of the per-row counts
-  unsigned* const fresh = reinterpret_cast<unsigned*>(row_off + BM + 1);   // [2*GROUPS] new-row bits per slot
+  int* const row_off = row_start + BM;     // [BM+1] exclusive prefix of the per-row counts, each rounded up to even
+  int* const row_cnt = row_off + BM + 1;   // [BM]   nonzeros of the row inside the tile
+  unsigned* const fresh = reinterpret_cast<unsigned*>(row_cnt + BM);   // [2*GROUPS] new-row bits per slot
   unsigned long long* const full = reinterpret_cast<unsigned long long*>(
       (reinterpret_cast<uintptr_t>(fresh + 2 * Cfg::GROUPS) + 7) & ~uintptr_t(7));
   unsigned long long* const empty = full + STAGES;
@@ -165,7 +166,12 @@ sddmm_sampled_kernel(const SddmmArgsT<T> a, const StagedGuard guard, int nb, int
       e = __ldg(p + 1);
     }
     row_start[tid] = s;
-    row_off[tid + 1] = e - s;
+    row_cnt[tid] = e - s;
+    // A row's slots start at an EVEN position (odd rows get one empty slot): a row can then change only at an
+    // even slot, and the K loop carries one predicated lhs load per TWO slots.  Measured
+    // (tools/ubench/ubench_lds_pred.cu): that load costs 4 cycles of the shared-memory pipe whenever any of the
+    // warp's four groups takes it and 1 cycle when none does -- next to the 4 cycles of the slot's rhs load.
+    row_off[tid + 1] = (e - s + 1) & ~1;
   }
   if (tid == 0) row_off[0] = 0;
   __syncthreads();
@@ -201,7 +207,7 @@ sddmm_sampled_kernel(const SddmmArgsT<T> a, const StagedGuard guard, int nb, int
 
   for (int lo = 0; lo < total; lo += CAP) {
     const int cnt_round = min(CAP, total - lo);
-    const int per = (cnt_round + Cfg::GROUPS - 1) / Cfg::GROUPS;  // slots in use per group (<= P)
+    const int per = ((cnt_round + Cfg::GROUPS - 1) / Cfg::GROUPS + 1) & ~1;  // slots in use per group (<= P), even
     const int nbatch = (per + 3) >> 2;                             // 4 slots per batch
 
     // ---- deal the round's nonzeros to (group, slot) ----
@@ -214,7 +220,7 @@ sddmm_sampled_kernel(const SddmmArgsT<T> a, const StagedGuard guard, int nb, int
     if (tid < 2 * Cfg::GROUPS) fresh[tid] = 0u;
     __syncthreads();
     for (int r = warp; r < BM; r += Cfg::THREADS / 32) {
-      const int off = row_off[r], cnt = row_off[r + 1] - off, s = row_start[r];
+      const int off = row_off[r], cnt = row_cnt[r], s = row_start[r];
       for (int i = lane; i < cnt; i += 32) {
         const int el = off + i - lo;
         if (el < 0 || el >= cnt_round) continue;
@@ -268,11 +274,9 @@ sddmm_sampled_kernel(const SddmmArgsT<T> a, const StagedGuard guard, int nb, int
           const unsigned fw = (4 * b < 32) ? f_lo : f_hi;
           if ((fw >> ((4 * b + 0) & 31)) & 1u) l = lds_u4(sl + ((uc.x & 0xfffu) << 4));
           acc[4 * b + 0] = dot_slab<T>(l, r0, acc[4 * b + 0]);
-          if ((fw >> ((4 * b + 1) & 31)) & 1u) l = lds_u4(sl + ((uc.y & 0xfffu) << 4));
-          acc[4 * b + 1] = dot_slab<T>(l, r1, acc[4 * b + 1]);
+          acc[4 * b + 1] = dot_slab<T>(l, r1, acc[4 * b + 1]);   // (odd slot: same row as the slot before)
           if ((fw >> ((4 * b + 2) & 31)) & 1u) l = lds_u4(sl + ((uc.z & 0xfffu) << 4));
           acc[4 * b + 2] = dot_slab<T>(l, r2, acc[4 * b + 2]);
-          if ((fw >> ((4 * b + 3) & 31)) & 1u) l = lds_u4(sl + ((uc.w & 0xfffu) << 4));
           acc[4 * b + 3] = dot_slab<T>(l, r3, acc[4 * b + 3]);
         }
       }
@@ -442,7 +446,7 @@ inline int sddmm_sampled_tile_width(const SddmmArgs& a, int replicas) {
   const int bn_max = a.n / 8 * 8 < 256 ? a.n / 8 * 8 : 256;
   for (int bn = 16; bn <= bn_max; bn += 8) {
     const double mu = (double)Cfg::BM * bn * density;
-    const double need = mu + 3.0 * sqrt(mu) + 1.0;
+    const double need = mu + 3.0 * sqrt(mu) + 1.0 + 0.5 * Cfg::BM;   // (+ half a slot per row: even-aligned rows)
     if (need > (double)Cfg::CAP && bn > 16) break;
     const int per = (int)ceil(need / Cfg::GROUPS);
     const int batches = (per + 3) / 4;
