@@ -299,3 +299,28 @@ def test_sddmm_reduce_unsorted_columns(ops, dev):
     scale = sum(oracle.sddmm_abs(256, 320, a.row_offsets, a.column_indices, lhs[r], rhs[r]).astype(np.float64)
                 for r in range(3))
     assert_close_fwd(got.cpu().numpy(), ref, scale, what="sddmm_reduce unsorted")
+
+
+@pytest.mark.parametrize("cfg", [1, 2])
+@pytest.mark.parametrize("m,n,k,density,reps", [(1000, 777, 520, 0.3, 1), (256, 192, 132, 0.6, 3), (130, 70, 4096, 0.9, 1)])
+def test_sddmm_tiled3_variant_matches_oracle(ops, dev, cfg, m, n, k, density, reps):
+    """The k-major dense-tile SDDMM (kernels/sddmm_tiled3.cuh, opt-in through the "sddmm_tiled3" knob): ragged
+    shapes, replicas, k not a multiple of the k-step -- against the fp64 oracle within the forward-error bound."""
+    a = random_csr(m, n, density, seed=m + k, values="pm1")
+    ri, ro, ci = (torch.from_numpy(x).to(dev) for x in (a.row_indices, a.row_offsets, a.column_indices))
+    shape_l = (reps, m, k) if reps > 1 else (m, k)
+    shape_r = (reps, n, k) if reps > 1 else (n, k)
+    lhs, rhs = dense_operand(shape_l, 5, "pm1"), dense_operand(shape_r, 6, "pm1")
+    ops.set_variant("sddmm", 2)
+    ops.set_variant("sddmm_tiled3", cfg)
+    try:
+        out = ops.sddmm(m, n, ri, ro, ci, torch.from_numpy(lhs).to(dev), torch.from_numpy(rhs).to(dev)).cpu().numpy()
+    finally:
+        ops.set_variant("sddmm_tiled3", 0)
+        ops.set_variant("sddmm", 0)
+    for r in range(reps):
+        l, rr = (lhs[r], rhs[r]) if reps > 1 else (lhs, rhs)
+        ref = oracle.sddmm(m, n, a.row_offsets, a.column_indices, l, rr).astype(np.float64)
+        scale = oracle.sddmm_abs(m, n, a.row_offsets, a.column_indices, l, rr)
+        got = out[r] if reps > 1 else out
+        assert np.all(np.abs(got - ref) <= 1e-5 * scale + 1e-30)

@@ -1,8 +1,4 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_sddmm.py tests/test_gpu_f16.py tests/test_gpu_plans.py tests/test_gpu_sharding.py tests/test_gpu_modules.py -q -x 2>&1 | tail -2
-for d in 0.02 0.05 0.1 0.15 0.2; do
-  python tools/prof_case.py sddmm $d 5 | tail -1
-  TSP_DTYPE=f16 python tools/prof_case.py sddmm $d 5 | tail -1
-done
+timeout 900 python -m pytest tests/test_gpu_sddmm.py -q -x 2>&1 | tail -2

@@ -18,7 +18,7 @@ n = int(sys.argv[4]) if len(sys.argv) > 4 else 4096
 dim = 4096
 if os.environ.get("TSP_VARIANT"):
     ops.set_variant(op if op in ("spmm", "sddmm") else "spmm", int(os.environ["TSP_VARIANT"]))
-for knob in ("sddmm_bn", "sddmm_p", "spmm_scb"):
+for knob in ("sddmm_bn", "sddmm_p", "spmm_scb", "sddmm_tiled3"):
     if os.environ.get("TSP_" + knob.upper()):
         ops.set_variant(knob, int(os.environ["TSP_" + knob.upper()]))
 dev = torch.device("cuda:0")

@@ -15,6 +15,7 @@
 #include "kernels/spmm_staged.cuh"
 #include "kernels/spmm_rowsplit.cuh"
 #include "kernels/sddmm_sampled.cuh"
+#include "kernels/sddmm_tiled3.cuh"
 #include "kernels/sddmm_rows.cuh"
 #include "kernels/attention_rows.cuh"
 #include "kernels/band.cuh"
@@ -33,6 +34,7 @@ std::atomic<int> g_transpose_variant{0};
 std::atomic<int> g_permute_cfg{0};
 std::atomic<int> g_permute_tiled{0};
 std::atomic<int> g_sddmm_b16{0};
+std::atomic<int> g_sddmm_tiled3{0};
 // 16-bit SDDMM: native sampled kernel below this density, widened fp32 tiled kernel above
 // (4096^3: 2.70 vs 2.96 ms at 35 %, 3.76 vs 2.96 at 50 %)
 constexpr double kSddmmB16SampledMaxDensity = 0.4;
@@ -94,6 +96,7 @@ int tsp_set_variant(const char* op, int variant) {
   if (op && strcmp(op, "permute") == 0) return g_permute_cfg.exchange(variant);
   if (op && strcmp(op, "permute_tiled") == 0) return g_permute_tiled.exchange(variant);
   if (op && strcmp(op, "sddmm_b16") == 0) return g_sddmm_b16.exchange(variant);
+  if (op && strcmp(op, "sddmm_tiled3") == 0) return g_sddmm_tiled3.exchange(variant);
   if (op && strcmp(op, "sddmm") == 0) return g_sddmm_variant.exchange(variant);
   if (op && strcmp(op, "sddmm_bn") == 0) return g_sddmm_bn.exchange(variant);
   if (op && strcmp(op, "sddmm_p") == 0) return g_sddmm_p.exchange(variant);
@@ -424,7 +427,9 @@ static int sddmm_staged(tsp_plan* plan, SddmmArgs& a, int replicas, cudaStream_t
   if (rc != 0) return rc + 1;
   if (!view) return -1;
   if ((rc = plan_flush_check(plan, stream)) != 0) return rc + 1;
-  rc = tiled ? launch_sddmm_tiled(a, replicas, stream, guard, view, tiled_v1)
+  const int t3 = g_sddmm_tiled3.load();
+  rc = tiled ? (t3 > 0 && !tiled_v1 ? launch_sddmm_tiled3(a, replicas, stream, guard, view, t3)
+                                    : launch_sddmm_tiled(a, replicas, stream, guard, view, tiled_v1))
              : launch_sddmm_sampled(a, replicas, stream, guard, bn, static_cast<const int*>(view), g_sddmm_p.load());
   if (rc != 0) return rc + 1;
   if (gs == kGuardSorted) return 0;
