@@ -14,7 +14,7 @@
 //  * one __syncthreads per k-step (double-buffered tiles), tiles walked in the L2-aware order of raster_tile.
 // Each output is ONE fp32 FMA chain in ascending k (the reference's order, sddmm/cuda_sddmm.cu.cc:117-139).
 // cuBLAS's SIMT SGEMM for the same contraction (A @ B^T, 4096^3) takes 2.40 ms on this GPU
-// (tools/ubench/sgemm_ceiling.py), sddmm_tiled2 2.76 ms, this kernel 2.86 ms: the synchronous LDG -> STS staging
+// (tools/ubench/sgemm_ceiling.py), sddmm_tiled2 2.76 ms, this kernel 2.83 ms: the synchronous LDG -> STS staging
 // and the barrier per k-step cost what the leaner accumulators win.  Kept as a measured alternative behind the
 // benchmark knob "sddmm_tiled3"; the dispatcher does not pick it.
 #pragma once
@@ -81,20 +81,39 @@ sddmm_tiled3_kernel(const SddmmArgs a, const StagedGuard guard, int col_blocks, 
       my_base = __ldg(bases + e);
     }
 
+    // Global addresses of the k-step's 16-byte pieces: two running pointers (advanced by BK per step, by the rest of
+    // the replica when the replica loop folded into the k loop wraps), a constant stride between a thread's
+    // pieces, and a per-tile bit per piece for rows / columns beyond the matrix -- recomputing
+    // ((replica * rows + row) * k + kk) per piece cost ~300 integer instructions per step and warp, a third of
+    // the warp's time (ncu source view).
     float4 ga[A_V4], gb[B_V4];
-    auto load_global = [&](int step) {
-      const int ks = step % ksteps1, rr = a.reduce_reps > 0 ? step / ksteps1 : rep;
-      const int kk = ks * BK + ld_kc * 4;
-      const bool kin = kk < a.k;
+    unsigned ok_a = 0, ok_b = 0;
 #pragma unroll
-      for (int q = 0; q < A_V4; ++q) {
-        const int row = rb * BM + ld_row + q * (128 / KV);
-        ga[q] = (kin && row < a.m) ? ldg_f4(a.lhs + ((size_t)rr * a.m + row) * a.k + kk) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
+    for (int q = 0; q < A_V4; ++q) ok_a |= (rb * BM + ld_row + q * (128 / KV) < a.m ? 1u : 0u) << q;
 #pragma unroll
-      for (int q = 0; q < B_V4; ++q) {
-        const int col = cb * BN + ld_row + q * (128 / KV);
-        gb[q] = (kin && col < a.n) ? ldg_f4(a.rhs + ((size_t)rr * a.n + col) * a.k + kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < B_V4; ++q) ok_b |= (cb * BN + ld_row + q * (128 / KV) < a.n ? 1u : 0u) << q;
+    const int rep0 = a.reduce_reps > 0 ? 0 : rep;
+    const float* pa = a.lhs + ((size_t)rep0 * a.m + (rb * BM + ld_row)) * a.k + ld_kc * 4;
+    const float* pb = a.rhs + ((size_t)rep0 * a.n + (cb * BN + ld_row)) * a.k + ld_kc * 4;
+    const long long stride = (long long)(128 / KV) * a.k;
+    const long long wrap_a = (long long)a.m * a.k - (long long)(ksteps1 - 1) * BK;
+    const long long wrap_b = (long long)a.n * a.k - (long long)(ksteps1 - 1) * BK;
+    int ks_next = 0;   // k-step (within the replica) the next load_global fetches
+    auto load_global = [&]() {
+      const bool kin = ks_next * BK + ld_kc * 4 < a.k;
+#pragma unroll
+      for (int q = 0; q < A_V4; ++q)
+        ga[q] = (kin && ((ok_a >> q) & 1u)) ? ldg_f4(pa + q * stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < B_V4; ++q)
+        gb[q] = (kin && ((ok_b >> q) & 1u)) ? ldg_f4(pb + q * stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (++ks_next == ksteps1) {
+        ks_next = 0;
+        pa += wrap_a;
+        pb += wrap_b;
+      } else {
+        pa += BK;
+        pb += BK;
       }
     };
     auto store_smem = [&](int buf) {
@@ -118,12 +137,12 @@ sddmm_tiled3_kernel(const SddmmArgs a, const StagedGuard guard, int col_blocks, 
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] = 0ull;
 
-    load_global(0);
+    load_global();
     store_smem(0);
     __syncthreads();
     const int ra0 = wr * 64 + ty * 4, cb0 = wc * 32 + tx * 4;
     for (int step = 0; step < nsteps; ++step) {
-      if (step + 1 < nsteps) load_global(step + 1);
+      if (step + 1 < nsteps) load_global();
       const float* const as = As + (step & 1) * BK * BM;
       const float* const bs = Bs + (step & 1) * BK * BN;
 #pragma unroll
@@ -202,7 +221,7 @@ inline int launch_sddmm_tiled3_cfg(const SddmmArgs& a, int replicas, cudaStream_
 }
 
 // knob "sddmm_tiled3": 1 = 16-deep k-steps, 2 = 32-deep k-steps (both 2 CTAs per SM; a 3-CTA build at <= 168
-// registers spills and is slower: 3.24 / 3.02 ms).  Measured at 4096^3: 2.97 / 2.86 ms against sddmm_tiled2's
+// registers spills and is slower: 3.24 / 3.02 ms).  Measured at 4096^3: 3.09 / 2.83 ms against sddmm_tiled2's
 // 2.76 ms -- an opt-in variant, not the default.
 inline int launch_sddmm_tiled3(const SddmmArgs& a, int replicas, cudaStream_t stream, const StagedGuard& guard,
                                const void* view, int cfg) {
