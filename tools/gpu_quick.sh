@@ -1,6 +1,6 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_sddmm.py -q -x -k tiled3 2>&1 | tail -2
-python tools/prof_case.py sddmm 0.5 3 | tail -1
-for v in 1 2; do TSP_SDDMM_TILED3=$v python tools/prof_case.py sddmm 0.5 3 | tail -1; done
+timeout 900 python -m pytest tests/test_gpu_softmax_transpose.py tests/test_gpu_f16.py tests/test_gpu_many_mask.py tests/test_gpu_attention.py -q -x 2>&1 | tail -2
+python tools/prof_c4.py softmax 128 5 | tail -1
+TSP_DTYPE=f16 python tools/prof_c4.py softmax 128 5 | tail -1

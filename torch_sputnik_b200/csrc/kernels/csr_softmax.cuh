@@ -1,8 +1,8 @@
 // csr_softmax.cuh -- row-wise softmax over CSR values (forward and backward), HBM-bound.
 //
 // Semantics of sputnik::SparseSoftmaxKernel (third_party/sputnik/sputnik/softmax/
-// sparse_softmax.cu.cc:24-69): per row, y = exp(x - max) * (1 / sum(exp(x - max))) with expf
-// and one reciprocal.  The reference makes three passes over the row from global memory and
+// sparse_softmax.cu.cc:24-69): per row, y = exp(x - max) * (1 / sum(exp(x - max))) with one reciprocal
+// (exp through the hardware EX2, see the kernel).  The reference makes three passes over the row from global memory and
 // launches once per replica (src/softmax_cuda.cu:35-43); here one warp keeps a row of up to
 // 32*REG values in registers so every value is read once and written once -- as aligned 16-byte
 // vectors (4 fp32 / 8 fp16 or bf16 values per lane-load) -- replicas ride on grid.y, and the
@@ -62,7 +62,9 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
   const size_t base = (size_t)mv.values + beg;
   const T* __restrict__ in = a.x + base;
   T* __restrict__ out = a.out + base;
-  const float scale = a.scale;
+  // exp(x) is evaluated as 2^(x log2 e) with the hardware EX2 (the reference uses expf, sparse_softmax.cu.cc:52;
+  // the difference is below 2 ulp of the probability): `scale` carries the log2 e, the maximum is in log2 units.
+  const float scale = a.scale * 1.4426950408889634f;
 
   // Vector path: the row is read and written as ALIGNED 16-byte vectors (4 fp32 / 8 16-bit values per lane
   // and load), starting at the 16-byte boundary at or before its first value; the up to V - 1 foreign
@@ -97,7 +99,7 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
       if (32 * j * V < vlen) {   // warp-uniform
 #pragma unroll
         for (int t = 0; t < V; ++t) {
-          v[j][t] = expf(v[j][t] - mx);   // expf(-inf) == 0 for masked slots
+          v[j][t] = exp2f(v[j][t] - mx);   // exp2f(-inf) == 0 for masked slots
           sum += v[j][t];
         }
       }
@@ -139,7 +141,7 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
 #pragma unroll
     for (int i = 0; i < REG; ++i) {
       if (32 * i < len) {        // warp-uniform: register slots past the row do no work
-        v[i] = expf(v[i] - mx);  // expf(-inf) == 0 for the padding lanes
+        v[i] = exp2f(v[i] - mx);  // exp2f(-inf) == 0 for the padding lanes
         sum += v[i];
       }
     }
@@ -155,11 +157,11 @@ __global__ void __launch_bounds__(WARPS * 32) csr_softmax_kernel(const SoftmaxAr
     for (int idx = lane; idx < len; idx += 32) mx = fmaxf(mx, Elem<T>::to_f(in[idx]) * scale);
     mx = warp_max(mx);
     float sum = 0.f;
-    for (int idx = lane; idx < len; idx += 32) sum += expf(Elem<T>::to_f(in[idx]) * scale - mx);
+    for (int idx = lane; idx < len; idx += 32) sum += exp2f(Elem<T>::to_f(in[idx]) * scale - mx);
     sum = warp_sum(sum);
     const float inv = 1.0f / sum;
     for (int idx = lane; idx < len; idx += 32)
-      out[idx] = Elem<T>::from_f(expf(Elem<T>::to_f(in[idx]) * scale - mx) * inv);
+      out[idx] = Elem<T>::from_f(exp2f(Elem<T>::to_f(in[idx]) * scale - mx) * inv);
   }
   }   // rows of this warp
 }
