@@ -9,7 +9,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "torch_sputnik_b200", "lib", "libtsp.so")
-WATCH = ("UTMALDG", "UBLKCP", "SYNCS", "FFMA2", "FFMA", "LDS", "LDG", "STG", "SHFL", "LDGSTS", "MUFU", "HMMA", "UTCMMA", "IMMA", "LDTM")
+WATCH = ("UTMALDG", "UBLKCP", "SYNCS", "FFMA2", "FHFMA", "FFMA", "LDS", "LDG", "STG", "SHFL", "LDGSTS", "MUFU", "HMMA", "UTCMMA", "IMMA", "LDTM")
 sass = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
 dem = {}
 counts = collections.OrderedDict()
@@ -44,4 +44,4 @@ for fam, g in groups.items():
     print(f"{fam[:34]:34s} {g['variants']:5d} {g['c']['_all']:8d} " + " ".join(f"{g['c'][w]:7d}" for w in WATCH))
 print(f"{'TOTAL':34s} {sum(g['variants'] for g in groups.values()):5d} {tot['_all']:8d} " + " ".join(f"{tot[w]:7d}" for w in WATCH))
 print("\nUTMALDG = cp.async.bulk.tensor (TMA tensor-map load), UBLKCP = cp.async.bulk (descriptor-free bulk copy), SYNCS = mbarrier,")
-print("FFMA2 = fma.rn.f32x2.  HMMA / UTCMMA / IMMA / LDTM (tensor-core / TMEM) must be 0: north_star excludes tensor cores for this path.")
+print("FFMA2 = fma.rn.f32x2, FHFMA = fma.rn.f32.f16 / .bf16 (16-bit factors, fp32 addend and result).  HMMA / UTCMMA / IMMA / LDTM (tensor-core / TMEM) must be 0: north_star excludes tensor cores for this path.")
