@@ -1,9 +1,12 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-cap() { local name=$1; shift; "$@" > gpurun_out/plain_$name.log 2>&1 || { echo "plain $name failed"; return; }; tail -1 gpurun_out/plain_$name.log
-  timeout 600 ncu --set full --clock-control none --import-source on --profile-from-start off -c 1 -f -o gpurun_out/$name "$@" > gpurun_out/ncu_$name.log 2>&1; echo "ncu $name rc=$?"; }
-cap r02_c4_softmax python tools/prof_c4.py softmax 128 2
-TSP_DTYPE=f16 cap r02_c4_softmax_f16 python tools/prof_c4.py softmax 128 2
-python tools/ncu_traffic.py gpurun_out gpurun_out > gpurun_out/traffic.log 2>&1
-rm -f gpurun_out/*.ncu-rep
+timeout 900 python -m pytest tests/test_gpu_sddmm.py tests/test_gpu_f16.py -q -x 2>&1 | tail -2
+for d in 0.02 0.05 0.1; do
+  python tools/prof_case.py sddmm $d 5 | tail -1
+  TSP_DTYPE=f16 python tools/prof_case.py sddmm $d 5 | tail -1
+done
+python tools/bench_configs.py --config C3 2>/dev/null | python -c "
+import sys, json
+for l in sys.stdin:
+    x=json.loads(l); print(x.get('op'), x.get('ms'))"
