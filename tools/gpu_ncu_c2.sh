@@ -26,4 +26,3 @@ TSP_DTYPE=f16 cap r02_c4_sddmm_rows_f16 python tools/prof_c4.py sddmm 32 2
 TSP_DTYPE=f16 cap r02_c4_spmm_rowsplit_f16 python tools/prof_c4.py spmm 32 2
 python tools/ncu_traffic.py gpurun_out gpurun_out > gpurun_out/traffic.log 2>&1; tail -3 gpurun_out/traffic.log
 rm -f gpurun_out/r02_c2_*.ncu-rep gpurun_out/r02_c4_spmm*.ncu-rep gpurun_out/r02_c4_softmax.ncu-rep gpurun_out/r02_c4_sddmm_rows*.ncu-rep
-timeout 600 python tools/train_dp_transformer.py --graph 0 --steps 5 > gpurun_out/r02_c5_eager_n1.json 2>> gpurun_out/c5.err; cat gpurun_out/r02_c5_eager_n1.json | cut -c1-200
